@@ -1,0 +1,179 @@
+// Lock-free, device-visible allocation tables.
+//
+// Every rank owns one shared-memory segment ("/ocm_<ns>tbl_r<rank>") holding a
+// header, one PoolDesc per tier (GPU HBM pool, pinned-host pool) and one Region
+// record per granule of each pool.  Rank 0 additionally owns the cluster table
+// ("/ocm_<ns>cluster") with per-rank capacity accounting.  All mutable words are
+// 32/64-bit atomics, so the daemon, every attached application and - once the
+// segment is cudaHostRegister'ed - device code can read and update them
+// without locks and without a daemon round trip.  ocm_alloc on the fast path
+// is therefore a handful of CAS operations and never issues a CUDA driver call
+// that could serialise with an in-flight copy (the reference calls
+// cudaMalloc/cudaFree per allocation, reference src/lib.c:240,365, and keeps
+// rank-0 bookkeeping in a mutex-protected list it never prunes,
+// src/alloc.c:133-137, src/mem.c:220-229).
+//
+// Allocator: size-class blocks (8 linear classes, then 4 per doubling) carved
+// from a bump frontier; freed blocks go to a per-class Treiber stack (ABA tag
+// in the upper half of the head word).  Freed blocks first pass through a
+// "dirty" stack so that the owner daemon can zero them (the reference
+// zero-fills remote buffers at allocation, src/alloc.c:171,
+// src/extoll_client.c:46 - here the cost is paid off the allocation path).
+#pragma once
+#include "msg.hpp"
+#include <atomic>
+#include <cstddef>
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace ocm {
+
+constexpr uint64_t kTableMagic   = 0x4F434D5441424C45ull; // "OCMTABLE"
+constexpr uint32_t kTableVersion = 3;
+constexpr int      kNumClasses   = 128;
+constexpr uint32_t kMaxGranules  = 1u << 18;
+
+enum RegionState : uint32_t { REGION_FREE = 0, REGION_LIVE = 1, REGION_DIRTY = 2, REGION_SCRUBBING = 3 };
+
+struct alignas(64) Region {
+    std::atomic<uint32_t> state;
+    uint32_t              cls_plus1;   // size class + 1 of the block starting here; 0 = never carved
+    std::atomic<uint32_t> next;        // stack link: granule index + 1, 0 = end
+    uint32_t              generation;
+    int32_t               owner_pid;
+    int32_t               owner_rank;
+    uint64_t              bytes;       // requested bytes
+    uint64_t              id;          // rem_alloc_id
+    std::atomic<uint64_t> signal;      // completion counter (puts add 1)
+    uint64_t              flags;
+    uint64_t              reserved;
+};
+static_assert(sizeof(Region) == 64, "one cache line per region");
+
+struct PoolDesc {
+    uint64_t bytes;            // capacity
+    uint64_t granule;          // bytes per granule (power of two)
+    uint32_t n_granules;
+    uint32_t tier;
+    uint64_t regions_offset;   // from segment start
+    std::atomic<uint64_t> frontier;      // granules handed out by the bump allocator
+    std::atomic<uint64_t> used_bytes;    // sum of live block bytes
+    std::atomic<uint64_t> live;
+    std::atomic<uint64_t> total_allocs;
+    std::atomic<uint64_t> total_frees;
+    std::atomic<uint64_t> dirty_head;    // {tag:32, idx+1:32}
+    std::atomic<uint64_t> dirty_bytes;
+    std::atomic<uint64_t> class_head[kNumClasses];
+};
+
+enum GpuShareMode : uint32_t { GPU_SHARE_NONE = 0, GPU_SHARE_VMM_FD = 1, GPU_SHARE_CUDA_IPC = 2 };
+
+struct TableHeader {
+    uint64_t magic;
+    uint32_t version;
+    int32_t  rank;
+    int32_t  n_ranks;
+    int32_t  daemon_pid;
+    int32_t  gpu_index;        // CUDA ordinal of the pool's GPU, -1 if none
+    uint32_t gpu_share_mode;   // GpuShareMode
+    uint8_t  cuda_ipc_handle[64];
+    uint8_t  gpu_uuid[16];
+    char     ns[32];
+    uint64_t segment_bytes;
+    std::atomic<uint32_t> ready;       // set last by the daemon
+    std::atomic<uint32_t> scrub_enabled;
+    std::atomic<uint64_t> next_id;
+    std::atomic<uint64_t> heartbeat_ns; // daemon liveness (CLOCK_MONOTONIC)
+    PoolDesc pool[TIER_COUNT];
+};
+
+struct NodeSlot {
+    std::atomic<uint32_t> joined;
+    int32_t  daemon_pid;
+    int32_t  gpu_index;
+    int32_t  num_gpu;
+    uint64_t pool_bytes[TIER_COUNT];
+    std::atomic<uint64_t> used[TIER_COUNT];   // reserved bytes, rank-0 capacity accounting
+    std::atomic<uint64_t> live;
+    uint64_t gpu_mem[kMaxGpus];
+    char     ip[64];
+};
+
+struct ClusterTable {
+    uint64_t magic;
+    uint32_t version;
+    int32_t  n_ranks;
+    std::atomic<uint32_t> ready;
+    uint32_t pad;
+    std::atomic<uint64_t> rr_cursor;
+    std::atomic<uint64_t> total_allocs;
+    std::atomic<uint64_t> total_frees;
+    std::atomic<uint64_t> rejected;
+    NodeSlot node[kMaxRanks];
+};
+
+// ---- size classes ------------------------------------------------------
+uint32_t class_granules(int cls);           // block size of a class, in granules
+int      class_of(uint64_t granules);       // smallest class that fits; -1 if none
+uint64_t default_granule(uint64_t pool_bytes, Tier tier);
+
+// ---- segment lifecycle (POSIX shm) ---------------------------------------
+struct ShmMapping {
+    void  *base = nullptr;
+    size_t bytes = 0;
+    int    fd = -1;
+    bool   owner = false;
+    std::string name;
+};
+// Create (O_EXCL unless replace) and size a segment; zero-filled.
+bool shm_create(const std::string &name, size_t bytes, bool replace, ShmMapping *out, std::string *err);
+bool shm_open_existing(const std::string &name, ShmMapping *out, std::string *err);
+void shm_close(ShmMapping *m, bool unlink_it);
+
+size_t table_segment_bytes(uint64_t gpu_pool_bytes, uint64_t host_pool_bytes,
+                           uint64_t gpu_granule = 0, uint64_t host_granule = 0);
+// Lay out a fresh (zeroed) segment.  Does not set ready.
+void table_format(void *base, size_t seg_bytes, int rank, int n_ranks, int daemon_pid,
+                  uint64_t gpu_pool_bytes, uint64_t host_pool_bytes,
+                  uint64_t gpu_granule = 0, uint64_t host_granule = 0);
+inline Region *table_regions(TableHeader *h, int tier) {
+    return reinterpret_cast<Region *>(reinterpret_cast<char *>(h) + h->pool[tier].regions_offset);
+}
+bool table_validate(const TableHeader *h, size_t mapped_bytes);
+
+// ---- lock-free pool operations (any process) ------------------------------
+struct BlockRef {
+    uint32_t region = 0;       // granule index of the block start
+    uint32_t generation = 0;
+    uint64_t offset = 0;       // byte offset in the pool
+    uint64_t block_bytes = 0;
+    uint64_t id = 0;
+};
+// 0 on success, OCM_ENOMEM / OCM_EINVAL (positive enum ocm_err values) otherwise.
+int pool_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int rank, BlockRef *out);
+// Releases a LIVE block whose id matches.  Returns OCM_ESTALE on double free /
+// id mismatch.  With scrubbing enabled the block is queued for the daemon.
+int pool_free(TableHeader *h, int tier, uint32_t region, uint64_t id);
+
+// ---- daemon-side maintenance ----------------------------------------------
+struct DirtyBlock { uint32_t region; uint64_t offset; uint64_t bytes; };
+// Detach the whole dirty stack (blocks become SCRUBBING).
+size_t pool_take_dirty(TableHeader *h, int tier, std::vector<DirtyBlock> *out);
+// Return a scrubbed block to its class stack.
+void pool_release_scrubbed(TableHeader *h, int tier, uint32_t region);
+// Walk carved blocks; for LIVE blocks call pred(owner_pid, owner_rank) and free
+// those for which it returns true.  Returns blocks reclaimed; adds their bytes
+// to *bytes_out.
+size_t pool_reclaim(TableHeader *h, int tier, bool (*pred)(int pid, int rank, void *ctx), void *ctx,
+                    uint64_t *bytes_out, std::vector<BlockRef> *reclaimed = nullptr);
+// Count LIVE blocks (O(blocks)); consistency checks for tests.
+size_t pool_count_live(TableHeader *h, int tier);
+
+// ---- cluster table / governor primitives -----------------------------------
+void cluster_format(ClusterTable *c, int n_ranks);
+// Reserve capacity on `rank`.  false if it would exceed the pool.
+bool cluster_reserve(ClusterTable *c, int rank, int tier, uint64_t bytes);
+void cluster_unreserve(ClusterTable *c, int rank, int tier, uint64_t bytes);
+
+} // namespace ocm

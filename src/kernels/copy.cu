@@ -1,0 +1,284 @@
+// K1/K2/K3 - contiguous one-sided put / get / third-party copy for sm_100a.
+//
+// Replaces the reference's data plane: ib_write/ib_read + ib_poll (reference
+// src/rdma.c:46-85,241-302), extoll_write/extoll_read with 2 x 8 MiB overlap
+// (src/extoll.c:40-173) and the staging memcpy/cudaMemcpy hops in ocm_copy
+// (src/lib.c:523-656).  Here one kernel moves the bytes end to end:
+//
+//  * bulk path: every warp of a persistent CTA runs an independent ring of
+//    `stages` tiles.  One elected lane issues cp.async.bulk global->shared
+//    (TMA engine, mbarrier complete_tx) and, when a tile has landed,
+//    cp.async.bulk shared->global to the destination - and optionally to a
+//    second destination, so a two-hop "window + far side" ocm_copy reads the
+//    source once.  Source and destination are generic addresses: local HBM,
+//    peer HBM over NVLink, or pinned host memory.  No SM registers touch the
+//    payload.
+//  * vector path: 16-byte LDG/STG grid-stride loop for small or oddly aligned
+//    transfers (lower latency than a trip through shared memory).
+//
+// Completion: the last CTA to finish (elected through a device-local ticket
+// word) adds 1 to the destination's signal word with release semantics at
+// system scope, after its own system fence.
+#include "kernels.h"
+#include "ptx.cuh"
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+
+namespace ocmk {
+
+constexpr int kMaxAgents = 8;
+constexpr int kMaxStages = 8;
+
+struct CopyArgs {
+    const uint8_t *src;
+    uint8_t       *dst;
+    uint8_t       *dst2;
+    uint64_t       bytes;
+    uint32_t       tile;
+    uint32_t       stages;
+    uint64_t      *signal;
+    unsigned      *ticket;
+};
+
+// Elect the last CTA and publish completion.  Called by one thread per CTA
+// after a CTA-wide barrier that follows the CTA's last store.
+__device__ __forceinline__ void finish_and_signal(uint64_t *signal, unsigned *ticket) {
+    __threadfence_system();
+    bool last = true;
+    if (gridDim.x > 1) {
+        if (ticket == nullptr) return; // nobody to notify
+        unsigned t = atomicAdd(ticket, 1u);
+        last = (t == gridDim.x - 1);
+        if (last) atomicExch(ticket, 0u); // ready for the next launch
+    }
+    if (last && signal) {
+        __threadfence_system();
+        red_release_sys_add(signal, 1ull);
+    }
+}
+
+__global__ void __launch_bounds__(kMaxAgents * 32, 1) ocm_copy_bulk_kernel(CopyArgs a) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) uint64_t full[kMaxAgents][kMaxStages];
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int agents = blockDim.x >> 5;
+    const uint32_t tile = a.tile, stages = a.stages;
+
+    if (lane == 0) {
+        for (uint32_t s = 0; s < stages; ++s) mbar_init(&full[warp][s], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    const uint64_t bulk_bytes = a.bytes & ~15ull;
+    const uint64_t n_tiles = (bulk_bytes + tile - 1) / tile;
+    const uint64_t ag = (uint64_t)blockIdx.x * agents + warp;
+    const uint64_t total = (uint64_t)gridDim.x * agents;
+
+    if (lane == 0 && ag < n_tiles) {
+        uint8_t *my = smem + (size_t)warp * stages * tile;
+        const uint64_t n_my = (n_tiles - ag + total - 1) / total;
+        auto tile_off = [&](uint64_t j) { return (ag + j * total) * (uint64_t)tile; };
+        auto tile_len = [&](uint64_t j) {
+            uint64_t off = tile_off(j);
+            return (uint32_t)(bulk_bytes - off < tile ? bulk_bytes - off : tile);
+        };
+        auto issue_load = [&](uint64_t j) {
+            uint32_t s = (uint32_t)(j % stages);
+            uint32_t len = tile_len(j);
+            mbar_arrive_expect_tx(&full[warp][s], len);
+            bulk_g2s(my + (size_t)s * tile, a.src + tile_off(j), len, &full[warp][s]);
+        };
+        const uint64_t npro = n_my < stages ? n_my : stages;
+        for (uint64_t j = 0; j < npro; ++j) issue_load(j);
+        for (uint64_t i = 0; i < n_my; ++i) {
+            uint32_t s = (uint32_t)(i % stages);
+            mbar_wait(&full[warp][s], (uint32_t)((i / stages) & 1));
+            uint64_t off = tile_off(i);
+            uint32_t len = tile_len(i);
+            bulk_s2g(a.dst + off, my + (size_t)s * tile, len);
+            if (a.dst2) bulk_s2g(a.dst2 + off, my + (size_t)s * tile, len);
+            bulk_commit();
+            // the store of tile i-1 has finished reading its stage once at most
+            // one group (tile i) is still pending: refill that stage
+            if (i >= 1 && i - 1 + stages < n_my) {
+                bulk_wait_read<1>();
+                issue_load(i - 1 + stages);
+            }
+        }
+        bulk_wait_all<0>();
+        fence_proxy_async_all();
+        __threadfence_system();
+    }
+    // tail (< 16 bytes) - plain byte stores by the first CTA
+    if (blockIdx.x == 0 && threadIdx.x < (a.bytes & 15ull)) {
+        uint64_t o = bulk_bytes + threadIdx.x;
+        uint8_t v = a.src[o];
+        a.dst[o] = v;
+        if (a.dst2) a.dst2[o] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) finish_and_signal(a.signal, a.ticket);
+}
+
+// Vector path.  V = access width in bytes (16, 8, 4 or 1): the widest power of
+// two dividing every pointer.
+template <typename VT>
+__global__ void __launch_bounds__(256) ocm_copy_vec_kernel(CopyArgs a) {
+    constexpr uint64_t V = sizeof(VT);
+    const uint64_t nvec = a.bytes / V;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const VT *__restrict__ s = reinterpret_cast<const VT *>(a.src);
+    VT *__restrict__ d = reinterpret_cast<VT *>(a.dst);
+    VT *__restrict__ d2 = reinterpret_cast<VT *>(a.dst2);
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    // 4 independent loads in flight per thread
+    for (; i + 3 * stride < nvec; i += 4 * stride) {
+        VT v0 = s[i], v1 = s[i + stride], v2 = s[i + 2 * stride], v3 = s[i + 3 * stride];
+        d[i] = v0; d[i + stride] = v1; d[i + 2 * stride] = v2; d[i + 3 * stride] = v3;
+        if (d2) { d2[i] = v0; d2[i + stride] = v1; d2[i + 2 * stride] = v2; d2[i + 3 * stride] = v3; }
+    }
+    for (; i < nvec; i += stride) {
+        VT v = s[i];
+        d[i] = v;
+        if (d2) d2[i] = v;
+    }
+    const uint64_t done = nvec * V;
+    if (blockIdx.x == 0 && threadIdx.x < a.bytes - done) {
+        uint8_t v = a.src[done + threadIdx.x];
+        a.dst[done + threadIdx.x] = v;
+        if (a.dst2) a.dst2[done + threadIdx.x] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) finish_and_signal(a.signal, a.ticket);
+}
+
+__global__ void ocm_signal_kernel(uint64_t *signal) {
+    __threadfence_system();
+    red_release_sys_add(signal, 1ull);
+}
+
+// ------------------------------------------------------------------ host ----
+int num_sms(int device) {
+    static int cached[64] = {0};
+    int dev = device;
+    if (dev < 0 && cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (dev >= 0 && dev < 64 && cached[dev]) return cached[dev];
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    if (dev >= 0 && dev < 64) cached[dev] = n;
+    return n;
+}
+
+static long env_long(const char *k, long dflt) {
+    const char *e = getenv(k);
+    if (!e || !*e) return dflt;
+    char *end = nullptr;
+    long v = strtol(e, &end, 0);
+    if (end && (*end == 'k' || *end == 'K')) v <<= 10;
+    if (end && (*end == 'm' || *end == 'M')) v <<= 20;
+    return v;
+}
+
+const CopyTuning &default_copy_tuning() {
+    static CopyTuning t = [] {
+        CopyTuning c;
+        if (const char *m = getenv("OCM_COPY_MODE")) {
+            if (!strcmp(m, "bulk")) c.mode = COPY_BULK;
+            else if (!strcmp(m, "vec")) c.mode = COPY_VEC;
+        }
+        c.ctas = (int)env_long("OCM_COPY_CTAS", c.ctas);
+        c.agents = (int)env_long("OCM_COPY_AGENTS", c.agents);
+        c.stages = (int)env_long("OCM_COPY_STAGES", c.stages);
+        c.tile_bytes = (int)env_long("OCM_COPY_TILE", c.tile_bytes);
+        c.bulk_min = (size_t)env_long("OCM_BULK_MIN", (long)c.bulk_min);
+        return c;
+    }();
+    return t;
+}
+
+static cudaError_t ensure_bulk_smem(size_t bytes) {
+    static size_t configured[64] = {0};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 64 && configured[dev] >= bytes) return cudaSuccess;
+    e = cudaFuncSetAttribute(ocm_copy_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess && dev < 64) configured[dev] = bytes;
+    return e;
+}
+
+cudaError_t launch_copy(void *dst, void *dst2, const void *src, size_t bytes, uint64_t *signal, unsigned *ticket,
+                        cudaStream_t stream, const CopyTuning *tuning, unsigned long long *launches) {
+    if (bytes == 0) {
+        if (signal) {
+            ocm_signal_kernel<<<1, 1, 0, stream>>>(signal);
+            if (launches) ++*launches;
+        }
+        return cudaGetLastError();
+    }
+    const CopyTuning &t = tuning ? *tuning : default_copy_tuning();
+    CopyArgs a;
+    a.src = static_cast<const uint8_t *>(src);
+    a.dst = static_cast<uint8_t *>(dst);
+    a.dst2 = static_cast<uint8_t *>(dst2);
+    a.bytes = bytes;
+    a.signal = signal;
+    a.ticket = ticket;
+    const uintptr_t align_or = (uintptr_t)src | (uintptr_t)dst | (uintptr_t)dst2;
+    const int sms = num_sms();
+
+    bool bulk = (align_or & 15) == 0 && bytes >= 16;
+    if (t.mode == COPY_VEC) bulk = false;
+    else if (t.mode == COPY_AUTO && bytes < t.bulk_min) bulk = false;
+
+    if (bulk) {
+        int agents = std::min(std::max(t.agents, 1), kMaxAgents);
+        int stages = std::min(std::max(t.stages, 2), kMaxStages);
+        size_t tile = ((size_t)std::max(t.tile_bytes, 1024) + 127) & ~(size_t)127;
+        while ((size_t)agents * stages * tile > (size_t)(224 << 10) && stages > 2) --stages;
+        while ((size_t)agents * stages * tile > (size_t)(224 << 10) && agents > 1) --agents;
+        while ((size_t)agents * stages * tile > (size_t)(224 << 10)) tile >>= 1;
+        a.tile = (uint32_t)tile;
+        a.stages = (uint32_t)stages;
+        uint64_t n_tiles = ((bytes & ~15ull) + tile - 1) / tile;
+        uint64_t want = (n_tiles + agents - 1) / agents;
+        int ctas = t.ctas > 0 ? t.ctas : sms;
+        if ((uint64_t)ctas > want) ctas = (int)want;
+        if (ctas < 1) ctas = 1;
+        if (ctas > 1 && signal && !ticket) return cudaErrorInvalidValue;
+        size_t smem = (size_t)agents * stages * tile;
+        cudaError_t e = ensure_bulk_smem(224 << 10);
+        if (e != cudaSuccess) return e;
+        ocm_copy_bulk_kernel<<<ctas, agents * 32, smem, stream>>>(a);
+    } else {
+        a.tile = 0;
+        a.stages = 0;
+        const int threads = 256;
+        int width = 16;
+        while (width > 1 && (align_or & (uintptr_t)(width - 1))) width >>= 1;
+        if (width == 2) width = 1;
+        uint64_t nvec = bytes / (uint64_t)width;
+        uint64_t want = (nvec + (uint64_t)threads * 4 - 1) / ((uint64_t)threads * 4);
+        int cap = t.ctas > 0 ? t.ctas : sms * 4;
+        int ctas = (int)std::min<uint64_t>(std::max<uint64_t>(want, 1), (uint64_t)cap);
+        if (ctas > 1 && signal && !ticket) return cudaErrorInvalidValue;
+        switch (width) {
+        case 16: ocm_copy_vec_kernel<uint4><<<ctas, threads, 0, stream>>>(a); break;
+        case 8: ocm_copy_vec_kernel<uint2><<<ctas, threads, 0, stream>>>(a); break;
+        case 4: ocm_copy_vec_kernel<uint32_t><<<ctas, threads, 0, stream>>>(a); break;
+        default: ocm_copy_vec_kernel<uint8_t><<<ctas, threads, 0, stream>>>(a); break;
+        }
+    }
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_signal(uint64_t *signal, cudaStream_t stream) {
+    ocm_signal_kernel<<<1, 1, 0, stream>>>(signal);
+    return cudaGetLastError();
+}
+
+} // namespace ocmk

@@ -1,0 +1,82 @@
+// Host-side launch interface of the sm_100a kernels.
+// Every launcher enqueues on `stream` and returns immediately.  Pointers may
+// be local HBM, peer HBM mapped into this process (NVLink), or pinned host
+// memory registered with CUDA - the kernels only see generic global addresses.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace ocmk {
+
+// ---- K1/K2/K3: contiguous put / get / third-party copy ----------------------
+enum CopyMode { COPY_AUTO = 0, COPY_BULK = 1, COPY_VEC = 2 };
+struct CopyTuning {
+    int mode = COPY_AUTO;
+    int ctas = 0;          // 0: derive from size and SM count
+    int agents = 4;        // independent TMA pipelines (warps) per CTA, <= 8
+    int stages = 3;        // ring depth per agent, <= 8
+    int tile_bytes = 16384;
+    size_t bulk_min = 128 << 10;   // below this the vector kernel is used
+};
+// Reads OCM_COPY_MODE / OCM_COPY_CTAS / OCM_COPY_AGENTS / OCM_COPY_STAGES /
+// OCM_COPY_TILE / OCM_BULK_MIN once.
+const CopyTuning &default_copy_tuning();
+
+// dst2 (optional) receives the same bytes (window + far side in one pass).
+// signal (optional): 64-bit counter, +1 with release.sys after the last byte.
+// ticket: zero-initialised device-local word used to elect the last CTA
+// (required when signal != nullptr and more than one CTA runs).
+// *launches (optional) is incremented by the number of kernels enqueued.
+cudaError_t launch_copy(void *dst, void *dst2, const void *src, size_t bytes, uint64_t *signal, unsigned *ticket,
+                        cudaStream_t stream, const CopyTuning *tuning = nullptr, unsigned long long *launches = nullptr);
+
+// ---- K9: fill / verify / checksum --------------------------------------------
+cudaError_t launch_fill(void *dst, size_t bytes, uint64_t pattern, cudaStream_t stream);
+// *mismatches (device or mapped host, u64) += number of 8-byte words != pattern (+ tail bytes)
+cudaError_t launch_verify(const void *p, size_t bytes, uint64_t pattern, unsigned long long *mismatches,
+                          cudaStream_t stream);
+// *sum (u64) += wrapping sum of all 8-byte words (tail bytes zero-extended)
+cudaError_t launch_checksum(const void *p, size_t bytes, unsigned long long *sum, cudaStream_t stream);
+// +1 (release.sys) on a signal word, ordered after prior work on the stream
+cudaError_t launch_signal(uint64_t *signal, cudaStream_t stream);
+
+// ---- K4/K5: strided pack/unpack with optional cast ----------------------------
+enum DType { DT_U8 = 0, DT_F32 = 1, DT_BF16 = 2, DT_F8E4M3 = 3 };
+struct StridedDesc {
+    const void *src;
+    void       *dst;
+    uint64_t    row_bytes;          // contiguous bytes per row on the source side
+    uint64_t    n[3];               // extents of the 3 outer dimensions (>= 1)
+    int64_t     src_stride[3];      // bytes
+    int64_t     dst_stride[3];      // bytes
+    int         src_dtype, dst_dtype;
+    int         scale_block;        // 32 or 128 when fp8 is involved
+    float      *scales;             // fp8 side: one fp32 per block, row-major over (rows, blocks)
+};
+cudaError_t launch_strided(const StridedDesc &d, uint64_t *signal, unsigned *ticket, cudaStream_t stream,
+                           unsigned long long *launches = nullptr);
+inline size_t dtype_size(int dt) { return dt == DT_F32 ? 4 : dt == DT_BF16 ? 2 : 1; }
+
+// ---- K6: replicated put ---------------------------------------------------------
+// One source, n_dst destinations (same bytes): a thread-block cluster shares
+// each staged tile (TMA cluster multicast) and every CTA stores to one replica.
+cudaError_t launch_put_replicated(void *const *dsts, int n_dst, const void *src, size_t bytes,
+                                  uint64_t *const *signals, unsigned *ticket, cudaStream_t stream);
+// NVLS variant: one multimem.st stream to a multicast VA.
+cudaError_t launch_put_multimem(void *mc_dst, const void *src, size_t bytes, uint64_t *mc_signal, unsigned *ticket,
+                                cudaStream_t stream);
+
+// ---- K7: GUPS over a striped table ------------------------------------------------
+struct GupsTable {
+    uint64_t *base[64];     // per-rank slab, mapped into this process
+    int       n_ranks;
+    uint64_t  words_per_stripe;   // power of two
+    uint64_t  total_words;        // power of two
+};
+cudaError_t launch_gups(const GupsTable &t, uint64_t n_updates, uint64_t seed, cudaStream_t stream);
+cudaError_t launch_gups_init(const GupsTable &t, int my_rank, cudaStream_t stream);
+
+int num_sms(int device = -1);
+
+} // namespace ocmk

@@ -1,0 +1,701 @@
+// libocm - application library (C ABI in include/oncillamem.h).
+//
+// Re-design of reference src/lib.c.  What stays: the twelve entry points, the
+// kinds, the "pair = local window + far side" model, the daemon hand-shake over
+// pmsg (MSG_CONNECT / MSG_CONNECT_CONFIRM / MSG_DISCONNECT, src/lib.c:98-165)
+// and the message-driven allocation protocol (src/lib.c:175-220,347-400).
+// What changes:
+//   * all memory - local kinds too - is sub-allocated from pools the rank
+//     daemons own and export (HBM via CUDA VMM, pinned host via shm), so
+//     ocm_alloc never calls cudaMalloc/cudaFree/malloc on the hot path;
+//   * fast path: placement + block reservation are CAS operations on the shared
+//     tables (common/tables.hpp), no daemon round trip; OCM_ALLOC_SLOW_PATH or
+//     OCM_ALLOC_PATH=daemon selects the full message protocol;
+//   * remote memory is mapped into this process once per rank and is then a
+//     plain pointer: there is no per-allocation connection (the reference builds
+//     one RC queue pair per allocation, src/rdma_client.c:40-179);
+//   * the defects listed in SURVEY Appendix B (#1-#5) are not reproduced.
+#include "ctx.hpp"
+#include "../common/governor.hpp"
+#include "../common/log.hpp"
+#include "../common/names.hpp"
+#include "../daemon/uds_proto.hpp"
+#include "../ipc/sock.hpp"
+#include <cerrno>
+#include <cstring>
+#include <cuda_runtime.h>
+#include <signal.h>
+#include <time.h>
+#include <unistd.h>
+
+using namespace ocm;
+
+namespace ocm {
+
+static thread_local int t_last_error = 0;
+void set_last_error(int e) { t_last_error = e; }
+
+Ctx &ctx() {
+    static Ctx *c = new Ctx(); // intentionally leaked: usable from atexit handlers
+    return *c;
+}
+
+static uint64_t mono_ns() {
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (uint64_t)ts.tv_sec * 1000000000ull + (uint64_t)ts.tv_nsec;
+}
+
+DeviceGuard::DeviceGuard(int dev) {
+    if (dev < 0) return;
+    if (cudaGetDevice(&prev) != cudaSuccess) {
+        prev = -1;
+        return;
+    }
+    if (prev != dev) {
+        cudaSetDevice(dev);
+        switched = true;
+    }
+}
+DeviceGuard::~DeviceGuard() {
+    if (switched && prev >= 0) cudaSetDevice(prev);
+}
+
+unsigned *next_ticket() {
+    Ctx &c = ctx();
+    if (!c.tickets) return nullptr;
+    return c.tickets + (c.ticket_cursor.fetch_add(1, std::memory_order_relaxed) % kNumTickets);
+}
+
+int daemon_call(Message &m, int timeout_ms) {
+    Ctx &c = ctx();
+    std::lock_guard<std::mutex> g(c.mq_mu);
+    m.pid = (int)getpid();
+    m.seq = ++c.seq;
+    uint16_t want_type = m.type == MSG_CONNECT ? (uint16_t)MSG_CONNECT_CONFIRM
+                         : (m.type == MSG_STATS || m.type == MSG_PING) ? m.type : (uint16_t)MSG_RELEASE_APP;
+    int r = c.box.send(c.daemon_mq, &m, timeout_ms);
+    if (r) {
+        LOGW("send to daemon failed: %s", strerror(-r));
+        return OCM_ENODAEMON;
+    }
+    uint64_t deadline = mono_ns() + (uint64_t)timeout_ms * 1000000ull;
+    for (;;) {
+        int64_t left = (int64_t)(deadline - mono_ns()) / 1000000;
+        if (left <= 0) return OCM_ENODAEMON;
+        Message rep;
+        r = c.box.recv(&rep, (int)std::min<int64_t>(left, 200));
+        if (r < 0) return OCM_ENODAEMON;
+        if (r == 0) {
+            // detect a dead daemon instead of waiting out the timeout
+            if (c.daemon_pid > 0 && kill(c.daemon_pid, 0) != 0 && errno == ESRCH) return OCM_ENODAEMON;
+            continue;
+        }
+        if (!rep.valid() || rep.seq != m.seq || rep.type != want_type) {
+            LOGW("unexpected reply %s seq %u (want %s seq %u) ignored", msg_type_str(rep.type), rep.seq,
+                 msg_type_str(want_type), m.seq);
+            continue;
+        }
+        m = rep;
+        return rep.err;
+    }
+}
+
+// ---------------------------------------------------------- mapping cache --
+static bool fetch_gpu_pool(int rank, RankView *v) {
+    Ctx &c = ctx();
+    std::string err;
+    TableHeader *h = v->hdr;
+    if (h->gpu_share_mode == GPU_SHARE_NONE || h->pool[TIER_GPU].bytes == 0) return false;
+    DeviceGuard dg(c.device);
+    if (h->gpu_share_mode == GPU_SHARE_CUDA_IPC) {
+        if (h->gpu_index != c.device) gpu::enable_peer_access(c.device, h->gpu_index);
+        if (!gpu::pool_import_ipc(h->cuda_ipc_handle, h->pool[TIER_GPU].bytes, h->gpu_index, c.device, &v->gpu, &err)) {
+            LOGE("rank %d HBM pool (cudaIpc): %s", rank, err.c_str());
+            return false;
+        }
+        return true;
+    }
+    int s = uds_connect(uds_name(rank), 2000);
+    if (s < 0) {
+        LOGE("cannot reach rank %d fd server: %s", rank, strerror(-s));
+        return false;
+    }
+    UdsRequest rq = {kUdsMagic, UDS_GET_GPU_POOL, (int32_t)getpid(), c.device};
+    UdsReply rp;
+    int fd = -1;
+    bool ok = sock_put(s, &rq, sizeof rq) == 1 && uds_recv_fd(s, &rp, sizeof rp, &fd, 5000) == 1;
+    sock_close(s);
+    if (!ok || rp.magic != kUdsMagic || rp.err || fd < 0) {
+        LOGE("rank %d did not hand out its HBM pool (err %d)", rank, ok ? rp.err : -1);
+        if (fd >= 0) close(fd);
+        return false;
+    }
+    ok = gpu::pool_import_fd(fd, rp.bytes, rp.owner_dev, c.device, &v->gpu, &err);
+    close(fd);
+    if (!ok) LOGE("rank %d HBM pool (vmm): %s", rank, err.c_str());
+    return ok;
+}
+
+RankView *get_view(int rank, bool with_gpu) {
+    Ctx &c = ctx();
+    if (rank < 0 || rank >= kMaxRanks) return nullptr;
+    RankView *v = &c.view[rank];
+    std::lock_guard<std::mutex> g(c.mu);
+    if (!v->tried) {
+        v->tried = true;
+        std::string err;
+        if (!shm_open_existing(shm_table_name(rank), &v->tbl_map, &err)) {
+            LOGW("rank %d tables: %s", rank, err.c_str());
+            return nullptr;
+        }
+        auto *h = static_cast<TableHeader *>(v->tbl_map.base);
+        if (!table_validate(h, v->tbl_map.bytes) || h->rank != rank) {
+            LOGE("rank %d tables: bad segment", rank);
+            shm_close(&v->tbl_map, false);
+            return nullptr;
+        }
+        v->hdr = h;
+        if (h->pool[TIER_HOST].bytes) {
+            if (!shm_open_existing(shm_host_pool_name(rank), &v->host_map, &err))
+                LOGW("rank %d host pool: %s", rank, err.c_str());
+        }
+        if (c.device >= 0) {
+            DeviceGuard dg(c.device);
+            // device-visible tables (signals) and zero-copy-capable host pool
+            if (!gpu::host_register(v->tbl_map.base, v->tbl_map.bytes, &err)) LOGW("%s", err.c_str());
+            if (v->host_map.base && !gpu::host_register(v->host_map.base, v->host_map.bytes, &err))
+                LOGW("%s", err.c_str());
+        }
+        v->ok = true;
+    }
+    if (!v->ok) return nullptr;
+    if (with_gpu && !v->gpu_tried && c.device >= 0) {
+        v->gpu_tried = true;
+        fetch_gpu_pool(rank, v);
+    }
+    return v;
+}
+
+static void drop_views() {
+    Ctx &c = ctx();
+    for (int r = 0; r < kMaxRanks; ++r) {
+        RankView &v = c.view[r];
+        if (v.gpu.ptr) gpu::pool_release(&v.gpu);
+        if (v.host_map.base) {
+            gpu::host_unregister(v.host_map.base);
+            shm_close(&v.host_map, false);
+        }
+        if (v.tbl_map.base) {
+            gpu::host_unregister(v.tbl_map.base);
+            shm_close(&v.tbl_map, false);
+        }
+        v = RankView();
+    }
+}
+
+// ------------------------------------------------------------ side helpers --
+static void *side_ptr(RankView *v, int tier, uint64_t offset) {
+    if (tier == TIER_HOST) return v->host_map.base ? (char *)v->host_map.base + offset : nullptr;
+    return v->gpu.ptr ? (char *)v->gpu.ptr + offset : nullptr;
+}
+
+static int release_side(Side &s);
+
+// Allocate one side through the shared tables (fast) or the daemon (slow).
+static int alloc_side(uint32_t type, uint64_t bytes, int policy, int explicit_rank, uint32_t flags, Side *out) {
+    Ctx &c = ctx();
+    const bool slow = c.force_slow || (flags & OCM_ALLOC_SLOW_PATH) || !c.cluster;
+    Allocation a;
+    memset(&a, 0, sizeof a);
+    if (!slow) {
+        AllocRequest req;
+        memset(&req, 0, sizeof req);
+        req.orig_rank = c.rank;
+        req.remote_rank = explicit_rank;
+        req.bytes = bytes;
+        req.type = type;
+        req.policy = (uint32_t)policy;
+        req.flags = flags;
+        int err = governor_place(c.cluster, req, &a);
+        if (err) return err;
+        RankView *v = get_view(a.remote_rank, a.tier == TIER_GPU);
+        BlockRef b;
+        err = v ? pool_alloc(v->hdr, (int)a.tier, bytes, (int)getpid(), c.rank, &b) : OCM_ENODAEMON;
+        if (err) {
+            governor_release(c.cluster, a.remote_rank, (int)a.tier, bytes);
+            return err;
+        }
+        a.rem_alloc_id = b.id; a.offset = b.offset; a.block_bytes = b.block_bytes;
+        a.region = b.region; a.generation = b.generation;
+        c.n_fast.fetch_add(1, std::memory_order_relaxed);
+    } else {
+        Message m;
+        m.init(MSG_REQ_ALLOC);
+        m.rank = c.rank;
+        m.u.req.orig_rank = c.rank;
+        m.u.req.remote_rank = explicit_rank;
+        m.u.req.bytes = bytes;
+        m.u.req.type = type;
+        m.u.req.policy = (uint32_t)policy;
+        m.u.req.flags = flags;
+        int err = daemon_call(m);
+        if (err) return err;
+        a = m.u.alloc;
+        c.n_slow.fetch_add(1, std::memory_order_relaxed);
+    }
+    RankView *v = get_view(a.remote_rank, a.tier == TIER_GPU);
+    out->backing = SIDE_POOL;
+    out->tier = (uint8_t)a.tier;
+    out->via_daemon = slow;
+    out->rank = a.remote_rank;
+    out->region = a.region;
+    out->generation = a.generation;
+    out->id = a.rem_alloc_id;
+    out->offset = a.offset;
+    out->bytes = bytes;
+    out->ptr = v ? side_ptr(v, (int)a.tier, a.offset) : nullptr;
+    out->rec = v ? &table_regions(v->hdr, (int)a.tier)[a.region] : nullptr;
+    if (!out->ptr) {
+        // reserved but not addressable from here (no GPU in this process / mapping failed)
+        release_side(*out);
+        *out = Side();
+        return a.tier == TIER_GPU ? OCM_ENOGPU : OCM_ENODAEMON;
+    }
+    c.bytes_live[a.tier].fetch_add(bytes, std::memory_order_relaxed);
+    return OCM_OK;
+}
+
+static int release_side(Side &s) {
+    Ctx &c = ctx();
+    int err = OCM_OK;
+    switch (s.backing) {
+    case SIDE_POOL:
+        if (!s.via_daemon && c.cluster) {
+            RankView *v = get_view(s.rank, false);
+            err = v ? pool_free(v->hdr, s.tier, s.region, s.id) : OCM_ENODAEMON;
+            if (!err) governor_release(c.cluster, s.rank, s.tier, s.bytes);
+        } else {
+            Message m;
+            m.init(MSG_REQ_FREE);
+            m.rank = c.rank;
+            Allocation &a = m.u.alloc;
+            a.orig_rank = c.rank; a.remote_rank = s.rank; a.rem_alloc_id = s.id; a.tier = s.tier;
+            a.type = s.tier == TIER_GPU ? ALLOC_MEM_REMOTE_GPU : ALLOC_MEM_REMOTE_HOST;
+            a.bytes = s.bytes; a.offset = s.offset; a.region = s.region; a.generation = s.generation;
+            err = daemon_call(m);
+        }
+        if (s.ptr) c.bytes_live[s.tier].fetch_sub(s.bytes, std::memory_order_relaxed);
+        break;
+    case SIDE_HEAP:
+        if (c.device >= 0) gpu::host_unregister(s.ptr);
+        free(s.ptr);
+        c.bytes_live[TIER_HOST].fetch_sub(s.bytes, std::memory_order_relaxed);
+        break;
+    case SIDE_CUDAMALLOC: {
+        DeviceGuard dg(c.device);
+        cudaFree(s.ptr);
+        c.bytes_live[TIER_GPU].fetch_sub(s.bytes, std::memory_order_relaxed);
+        break;
+    }
+    default: break;
+    }
+    s = Side();
+    return err;
+}
+
+// Local side with the reference's fallbacks (malloc / cudaMalloc, src/lib.c:226,240)
+// when the rank's pool cannot serve the request.
+static int alloc_local_side(int tier, uint64_t bytes, uint32_t flags, Side *out) {
+    Ctx &c = ctx();
+    if (tier == TIER_GPU && c.device < 0) return OCM_ENOGPU;
+    int err = alloc_side(tier == TIER_GPU ? ALLOC_MEM_GPU : ALLOC_MEM_HOST, bytes, OCM_POLICY_SELF, c.rank, flags, out);
+    if (!err) return OCM_OK;
+    if (err != OCM_ENOMEM && err != OCM_ENOGPU && err != OCM_ENODAEMON) return err;
+    if (tier == TIER_HOST) {
+        void *p = nullptr;
+        if (posix_memalign(&p, 4096, bytes ? bytes : 1)) return OCM_ENOMEM;
+        if (!(flags & OCM_ALLOC_NO_ZERO)) memset(p, 0, bytes);
+        out->backing = SIDE_HEAP;
+        out->ptr = p;
+    } else {
+        DeviceGuard dg(c.device);
+        void *p = nullptr;
+        if (cudaMalloc(&p, bytes ? bytes : 1) != cudaSuccess) {
+            cudaGetLastError();
+            return OCM_ENOMEM;
+        }
+        if (!(flags & OCM_ALLOC_NO_ZERO)) cudaMemset(p, 0, bytes);
+        out->backing = SIDE_CUDAMALLOC;
+        out->ptr = p;
+    }
+    out->tier = (uint8_t)tier;
+    out->rank = c.rank;
+    out->bytes = bytes;
+    c.bytes_live[tier].fetch_add(bytes, std::memory_order_relaxed);
+    return OCM_OK;
+}
+
+static bool valid_handle(ocm_alloc_t a) { return a && a->magic == kAllocMagic; }
+
+} // namespace ocm
+
+// ============================================================ public API ===
+extern "C" {
+
+int ocm_last_error(void) { return t_last_error; }
+
+int ocm_init(void) {
+    Ctx &c = ctx();
+    {
+        std::lock_guard<std::mutex> g(c.mu);
+        if (c.inited) return 0;
+    }
+    set_log_tag("app");
+    const char *er = getenv("OCM_RANK");
+    int want_rank = er ? atoi(er) : 0;
+    c.daemon_mq = mq_daemon_name(want_rank);
+    const char *ap = getenv("OCM_ALLOC_PATH");
+    c.force_slow = ap && (!strcmp(ap, "daemon") || !strcmp(ap, "slow"));
+    const char *et = getenv("OCM_INIT_TIMEOUT_MS");
+    int timeout_ms = et ? atoi(et) : 5000;
+
+    int r = c.box.open(mq_app_name((int)getpid()), sizeof(Message), 8, true);
+    if (r) {
+        set_last_error(OCM_ENODAEMON);
+        return -1;
+    }
+    // attach with retries (reference: 10 x 10 ms with an unconditional first sleep, src/lib.c:111-115)
+    uint64_t deadline = mono_ns() + (uint64_t)timeout_ms * 1000000ull;
+    bool attached = false;
+    while (!(attached = c.box.attach(c.daemon_mq) == 0) && mono_ns() < deadline) usleep(1000);
+    if (!attached) {
+        LOGE("no daemon mailbox %s", c.daemon_mq.c_str());
+        c.box.close(true);
+        set_last_error(OCM_ENODAEMON);
+        return -1;
+    }
+    Message m;
+    int err = OCM_ENODAEMON;
+    while (mono_ns() < deadline) {
+        m.init(MSG_CONNECT);
+        err = daemon_call(m, 2000);
+        if (err != OCM_ENODAEMON) break;   // ENODAEMON in the confirm = daemon not joined yet
+        usleep(5000);
+    }
+    if (err) {
+        LOGE("daemon hand-shake failed: %s", ocm_strerror(err));
+        c.box.detach(c.daemon_mq);
+        c.box.close(true);
+        set_last_error(err);
+        return -1;
+    }
+    c.rank = m.u.conn.rank;
+    c.n_ranks = m.u.conn.n_ranks;
+    c.daemon_pid = m.u.conn.daemon_pid;
+    for (auto &b : c.bytes_live) b.store(0);
+
+    // GPU of this process: OCM_DEVICE > the rank's GPU > current device
+    c.device = -1;
+    if (gpu::device_count() > 0) {
+        const char *ed = getenv("OCM_DEVICE");
+        int dev = ed ? atoi(ed) : (m.u.conn.gpu_index >= 0 ? m.u.conn.gpu_index : gpu::current_device());
+        if (dev >= 0 && dev < gpu::device_count()) {
+            DeviceGuard dg(dev);
+            if (cudaFree(0) == cudaSuccess) {
+                c.device = dev;
+                cudaStream_t s;
+                if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) == cudaSuccess) c.stream = s;
+                if (cudaMalloc((void **)&c.tickets, kNumTickets * sizeof(unsigned)) == cudaSuccess)
+                    cudaMemset(c.tickets, 0, kNumTickets * sizeof(unsigned));
+                else c.tickets = nullptr;
+            } else {
+                cudaGetLastError();
+            }
+        }
+    }
+    std::string e2;
+    if (shm_open_existing(shm_cluster_name(), &c.cluster_map, &e2)) {
+        auto *ct = static_cast<ClusterTable *>(c.cluster_map.base);
+        if (c.cluster_map.bytes >= sizeof(ClusterTable) && ct->magic == kTableMagic && ct->version == kTableVersion)
+            c.cluster = ct;
+    }
+    if (!c.cluster) LOGI("cluster table not mapped: allocations use the daemon protocol");
+    {
+        std::lock_guard<std::mutex> g(c.mu);
+        c.inited = true;
+    }
+    get_view(c.rank, c.device >= 0);
+    LOGD("attached to rank %d/%d, device %d, %s path", c.rank, c.n_ranks, c.device,
+         (c.cluster && !c.force_slow) ? "fast" : "daemon");
+    return 0;
+}
+
+int ocm_tini(void) {
+    Ctx &c = ctx();
+    {
+        std::lock_guard<std::mutex> g(c.mu);
+        if (!c.inited) return -1;
+    }
+    // release what the application forgot (the reference leaks it, src/lib.c:147-165)
+    std::vector<lib_alloc *> left;
+    {
+        std::lock_guard<std::mutex> g(c.mu);
+        left.assign(c.allocs.begin(), c.allocs.end());
+    }
+    if (!left.empty()) LOGW("%zu allocation(s) still live at ocm_tini: releasing", left.size());
+    for (auto *a : left) ocm_free(a);
+    if (c.device >= 0) {
+        DeviceGuard dg(c.device);
+        if (c.stream) {
+            cudaStreamSynchronize((cudaStream_t)c.stream);
+            cudaStreamDestroy((cudaStream_t)c.stream);
+        }
+        if (c.tickets) cudaFree(c.tickets);
+        c.stream = nullptr;
+        c.tickets = nullptr;
+    }
+    Message m;
+    m.init(MSG_DISCONNECT);
+    m.pid = (int)getpid();
+    int ret = 0;
+    if (c.box.send(c.daemon_mq, &m, 1000)) ret = -1;
+    c.box.detach(c.daemon_mq);
+    c.box.close(true);
+    drop_views();
+    if (c.cluster_map.base) shm_close(&c.cluster_map, false);
+    c.cluster = nullptr;
+    {
+        std::lock_guard<std::mutex> g(c.mu);
+        c.inited = false;
+    }
+    return ret;
+}
+
+enum ocm_kind ocm_alloc_kind(ocm_alloc_t a) { return valid_handle(a) ? a->kind : (enum ocm_kind)0; }
+
+ocm_alloc_t ocm_alloc_ex(const struct ocm_alloc_params_ex *p) {
+    Ctx &c = ctx();
+    if (!p || !c.inited) {
+        set_last_error(c.inited ? OCM_EINVAL : OCM_ENODAEMON);
+        return nullptr;
+    }
+    const enum ocm_kind kind = p->base.kind;
+    const uint32_t flags = p->flags;
+    lib_alloc *a = new lib_alloc();
+    a->magic = kAllocMagic;
+    a->kind = kind;
+    a->paired = false;
+    a->stripe_bytes = 0;
+    a->lib_stream_pending.store(false);
+    int err = OCM_OK;
+
+    switch (kind) {
+    case OCM_LOCAL_HOST:
+    case OCM_LOCAL_RMA:
+    case OCM_LOCAL_RDMA:
+        a->kind = OCM_LOCAL_HOST;
+        err = alloc_local_side(TIER_HOST, p->base.local_alloc_bytes, flags, &a->local);
+        break;
+    case OCM_LOCAL_GPU:
+        err = alloc_local_side(TIER_GPU, p->base.local_alloc_bytes, flags, &a->local);
+        break;
+    case OCM_REMOTE_RDMA:
+    case OCM_REMOTE_RMA:
+    case OCM_REMOTE_HOST:
+    case OCM_REMOTE_GPU: {
+        a->paired = true;
+        const bool gpu_kind = kind == OCM_REMOTE_GPU;
+        if (gpu_kind && c.device < 0) { err = OCM_ENOGPU; break; }
+        uint32_t type = gpu_kind ? ALLOC_MEM_REMOTE_GPU
+                        : kind == OCM_REMOTE_RDMA ? ALLOC_MEM_RDMA
+                        : kind == OCM_REMOTE_RMA ? ALLOC_MEM_RMA : ALLOC_MEM_REMOTE_HOST;
+        err = alloc_side(type, p->base.rem_alloc_bytes, p->policy, p->rank, flags, &a->remote);
+        if (err) break;
+        if (gpu_kind && a->remote.tier != TIER_GPU) a->kind = OCM_REMOTE_HOST; // downgraded by the governor
+        if (!(flags & OCM_ALLOC_NO_WINDOW) && p->base.local_alloc_bytes) {
+            err = alloc_local_side(gpu_kind ? TIER_GPU : TIER_HOST, p->base.local_alloc_bytes, flags, &a->local);
+            if (err) release_side(a->remote);
+        }
+        break;
+    }
+    case OCM_STRIPED_GPU:
+    case OCM_REPLICATED_GPU: {
+        // one far-side slab per rank: striped = 1/N of the bytes each, replicated = all bytes each
+        a->paired = true;
+        if (c.device < 0) { err = OCM_ENOGPU; break; }
+        const int N = c.n_ranks;
+        uint64_t per = kind == OCM_STRIPED_GPU ? (p->base.rem_alloc_bytes + N - 1) / N : p->base.rem_alloc_bytes;
+        per = (per + 255) & ~255ull;
+        a->stripe_bytes = per;
+        a->stripes.resize(N);
+        for (int r = 0; r < N && !err; ++r)
+            err = alloc_side(ALLOC_MEM_REMOTE_GPU, per, OCM_POLICY_EXPLICIT, r, flags, &a->stripes[r]);
+        for (int r = 0; r < N && !err; ++r)
+            if (a->stripes[r].tier != TIER_GPU) err = OCM_ENOGPU;
+        if (!err && !(flags & OCM_ALLOC_NO_WINDOW) && p->base.local_alloc_bytes)
+            err = alloc_local_side(TIER_GPU, p->base.local_alloc_bytes, flags, &a->local);
+        if (err)
+            for (auto &s : a->stripes)
+                if (s.valid()) release_side(s);
+        break;
+    }
+    default:
+        LOGW("ocm_alloc: no allocation type specified (kind %d)", (int)kind);
+        err = OCM_EINVAL;
+        break;
+    }
+    if (err) {
+        a->magic = 0;
+        delete a;
+        set_last_error(err);
+        return nullptr;
+    }
+    {
+        std::lock_guard<std::mutex> g(c.mu);
+        c.allocs.insert(a);   // every kind is tracked (the reference skips LOCAL_HOST)
+    }
+    c.n_alloc.fetch_add(1, std::memory_order_relaxed);
+    set_last_error(0);
+    return a;
+}
+
+ocm_alloc_t ocm_alloc(ocm_alloc_param_t alloc_param) {
+    if (!alloc_param) {
+        set_last_error(OCM_EINVAL);
+        return nullptr;
+    }
+    struct ocm_alloc_params_ex ex;
+    memset(&ex, 0, sizeof ex);
+    ex.base = *alloc_param;
+    ex.policy = OCM_POLICY_DEFAULT;
+    ex.rank = -1;
+    return ocm_alloc_ex(&ex);
+}
+
+int ocm_free(ocm_alloc_t a) {
+    Ctx &c = ctx();
+    if (!valid_handle(a)) {   // NULL and double frees are rejected (reference derefs first, App. B #2)
+        set_last_error(OCM_ESTALE);
+        return -1;
+    }
+    {
+        std::lock_guard<std::mutex> g(c.mu);
+        if (!c.allocs.erase(a)) {
+            set_last_error(OCM_ESTALE);
+            return -1;
+        }
+    }
+    if (a->lib_stream_pending.load() && c.stream) {
+        DeviceGuard dg(c.device);
+        cudaStreamSynchronize((cudaStream_t)c.stream);
+    }
+    int err = OCM_OK;
+    if (a->local.valid()) err = release_side(a->local);
+    if (a->remote.valid()) {
+        int e2 = release_side(a->remote);
+        if (!err) err = e2;
+    }
+    for (auto &s : a->stripes)
+        if (s.valid()) {
+            int e2 = release_side(s);
+            if (!err) err = e2;
+        }
+    a->magic = 0;
+    delete a;
+    c.n_free.fetch_add(1, std::memory_order_relaxed);
+    set_last_error(err);
+    return err ? -1 : 0;
+}
+
+int ocm_localbuf(ocm_alloc_t a, void **buf, size_t *len) {
+    if (!valid_handle(a) || !buf || !len) return -1;
+    *buf = a->local.ptr;
+    *len = (size_t)a->local.bytes;
+    return a->local.valid() ? 0 : -1;
+}
+
+bool ocm_is_remote(ocm_alloc_t a) { return valid_handle(a) && a->paired; }
+
+int ocm_remote_sz(ocm_alloc_t a, size_t *len) {
+    if (!valid_handle(a) || !len || !a->paired) return -1;
+    if (!a->stripes.empty())
+        *len = (size_t)(a->kind == OCM_STRIPED_GPU ? a->stripe_bytes * a->stripes.size() : a->stripe_bytes);
+    else *len = (size_t)a->remote.bytes;
+    return 0;
+}
+
+int ocm_rank(void) { return ctx().inited ? ctx().rank : -1; }
+int ocm_num_ranks(void) { return ctx().inited ? ctx().n_ranks : -1; }
+int ocm_device(void) { return ctx().inited ? ctx().device : -1; }
+int ocm_remote_rank(ocm_alloc_t a) { return valid_handle(a) && a->paired && a->stripes.empty() ? a->remote.rank : -1; }
+void *ocm_remote_ptr(ocm_alloc_t a) { return valid_handle(a) && a->paired && a->stripes.empty() ? a->remote.ptr : nullptr; }
+uint64_t ocm_alloc_id(ocm_alloc_t a) {
+    if (!valid_handle(a)) return 0;
+    return a->paired && a->stripes.empty() ? a->remote.id : a->local.id;
+}
+
+int ocm_signal_read(ocm_alloc_t a, uint64_t *value) {
+    if (!valid_handle(a) || !value) return -OCM_EINVAL;
+    const Side &s = (a->paired && a->remote.valid()) ? a->remote : a->local;
+    if (!s.rec) return -OCM_EUNSUPPORTED;
+    *value = s.rec->signal.load(std::memory_order_acquire);
+    return 0;
+}
+
+int ocm_signal_wait(ocm_alloc_t a, uint64_t at_least, int timeout_ms) {
+    if (!valid_handle(a)) return -OCM_EINVAL;
+    const Side &s = (a->paired && a->remote.valid()) ? a->remote : a->local;
+    if (!s.rec) return -OCM_EUNSUPPORTED;
+    uint64_t deadline = mono_ns() + (uint64_t)(timeout_ms < 0 ? 0 : timeout_ms) * 1000000ull;
+    for (unsigned spin = 0;; ++spin) {
+        if (s.rec->signal.load(std::memory_order_acquire) >= at_least) return 0;
+        if (timeout_ms >= 0 && mono_ns() > deadline) return -OCM_ESTALE;
+        if (spin > 1000) usleep(20);
+    }
+}
+
+int ocm_get_stats(struct ocm_stats *out) {
+    Ctx &c = ctx();
+    if (!out || !c.inited) return -OCM_EINVAL;
+    memset(out, 0, sizeof *out);
+    out->allocs_total = c.n_alloc.load();
+    out->frees_total = c.n_free.load();
+    out->allocs_live = out->allocs_total - out->frees_total;
+    out->bytes_gpu_live = c.bytes_live[TIER_GPU].load();
+    out->bytes_host_live = c.bytes_live[TIER_HOST].load();
+    out->copies = c.n_copies.load();
+    out->copy_bytes = c.copy_bytes.load();
+    out->kernel_launches = c.kernel_launches;
+    out->fast_path_allocs = c.n_fast.load();
+    out->slow_path_allocs = c.n_slow.load();
+    if (RankView *v = get_view(c.rank, false)) {
+        out->pool_gpu_bytes = v->hdr->pool[TIER_GPU].bytes;
+        out->pool_gpu_used = v->hdr->pool[TIER_GPU].used_bytes.load();
+        out->pool_host_bytes = v->hdr->pool[TIER_HOST].bytes;
+        out->pool_host_used = v->hdr->pool[TIER_HOST].used_bytes.load();
+    }
+    return 0;
+}
+
+int ocm_get_rank_stats(int rank, struct ocm_stats *out) {
+    Ctx &c = ctx();
+    if (!out || !c.inited) return -OCM_EINVAL;
+    Message m;
+    m.init(MSG_STATS);
+    m.rank = rank;
+    int err = daemon_call(m);
+    if (err) return -err;
+    memset(out, 0, sizeof *out);
+    const StatsPayload &s = m.u.stats;
+    out->allocs_live = s.allocs_live;
+    out->allocs_total = s.allocs_total;
+    out->frees_total = s.frees_total;
+    out->pool_gpu_bytes = s.pool_bytes[TIER_GPU];
+    out->pool_gpu_used = s.pool_used[TIER_GPU];
+    out->pool_host_bytes = s.pool_bytes[TIER_HOST];
+    out->pool_host_used = s.pool_used[TIER_HOST];
+    return 0;
+}
+
+} // extern "C"

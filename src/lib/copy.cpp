@@ -1,0 +1,301 @@
+// Copy engine of libocm: ocm_copy / ocm_copy_onesided / ocm_copy_in / ocm_copy_out
+// and their stream-ordered and strided variants.
+//
+// The reference implements a sparse kind matrix with serial blocking hops
+// (memcpy -> ib_write -> ib_poll, cudaMemcpy -> ib_write, ...; reference
+// src/lib.c:502-723) and BUG()s on remote<->remote, silently skips
+// GPU->GPU.  Here every allocation side is a generic address in this process,
+// so any (source side, destination side) combination is one primitive:
+//   GPU<->GPU (same or peer device)     our sm_100a copy kernel over NVLink
+//   window + far side in one pass        the same kernel with two destinations
+//   pinned host -> {GPU window, far GPU} zero-copy read fused into that kernel
+//   plain host<->GPU                     cudaMemcpyAsync on the stream (host tier only)
+//   host<->host                          memcpy
+// Offsets: src_offset/dest_offset drive the first hop, src_offset_2/dest_offset_2
+// the second; when the second hop starts where the first one landed
+// the two hops are fused.
+#include "ctx.hpp"
+#include "../common/log.hpp"
+#include "../kernels/kernels.h"
+#include <cstring>
+#include <cuda_runtime.h>
+
+using namespace ocm;
+
+namespace ocm {
+
+static bool kernel_addressable(const Side &s) {
+    if (s.tier == TIER_GPU) return true;
+    return s.backing == SIDE_POOL; // pool host memory is pinned + mapped in this process
+}
+
+static int cuda_err(cudaError_t e, const char *what) {
+    if (e == cudaSuccess) return OCM_OK;
+    LOGE("%s: %s", what, cudaGetErrorString(e));
+    cudaGetLastError();
+    return OCM_ECUDA;
+}
+
+static int single_copy(const Side &dst, uint64_t dst_off, const Side &src, uint64_t src_off, uint64_t bytes,
+                       cudaStream_t st, bool *used_stream, uint64_t *signal, bool *signalled) {
+    Ctx &c = ctx();
+    char *d = (char *)dst.ptr + dst_off;
+    const char *s = (const char *)src.ptr + src_off;
+    if (dst.tier == TIER_HOST && src.tier == TIER_HOST) {
+        // a previous hop on the stream may still be producing the source
+        if (*used_stream) {
+            cudaStreamSynchronize(st);
+        }
+        memcpy(d, s, bytes);
+        return OCM_OK;
+    }
+    if (c.device < 0) return OCM_ENOGPU;
+    *used_stream = true;
+    if (dst.tier == TIER_GPU && src.tier == TIER_GPU) {
+        *signalled = signal != nullptr;
+        return cuda_err(ocmk::launch_copy(d, nullptr, s, bytes, signal, next_ticket(), st, nullptr, &c.kernel_launches),
+                        "copy kernel");
+    }
+    // host tier <-> GPU: copy engine (H1)
+    return cuda_err(cudaMemcpyAsync(d, s, bytes, dst.tier == TIER_GPU ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost, st),
+                    "cudaMemcpyAsync");
+}
+
+int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2_off, const Side &src, uint64_t src_off,
+              uint64_t bytes, Region *signal_rec, void *stream, bool *used_stream) {
+    Ctx &c = ctx();
+    if (!dst.ptr || !src.ptr || (dst2 && !dst2->ptr)) return OCM_EINVAL;
+    if (src_off + bytes > src.bytes || dst_off + bytes > dst.bytes || (dst2 && dst2_off + bytes > dst2->bytes))
+        return OCM_ERANGE;
+    c.n_copies.fetch_add(1, std::memory_order_relaxed);
+    c.copy_bytes.fetch_add(bytes, std::memory_order_relaxed);
+    uint64_t *signal = signal_rec ? reinterpret_cast<uint64_t *>(&signal_rec->signal) : nullptr;
+    cudaStream_t st = (cudaStream_t)(stream ? stream : c.stream);
+
+    const bool all_host = src.tier == TIER_HOST && dst.tier == TIER_HOST && (!dst2 || dst2->tier == TIER_HOST);
+    if (all_host) {
+        if (*used_stream) {
+            DeviceGuard dg(c.device);
+            cudaStreamSynchronize(st);
+        }
+        const char *s = (const char *)src.ptr + src_off;
+        memcpy((char *)dst.ptr + dst_off, s, bytes);
+        if (dst2) memcpy((char *)dst2->ptr + dst2_off, s, bytes);
+        if (signal_rec) signal_rec->signal.fetch_add(1, std::memory_order_release);
+        return OCM_OK;
+    }
+    if (c.device < 0) return OCM_ENOGPU;
+    DeviceGuard dg(c.device);
+    bool signalled = false;
+    int err = OCM_OK;
+
+    // fused path: one kernel reads the source once and feeds every destination
+    const bool gpu_dst = dst.tier == TIER_GPU || (dst2 && dst2->tier == TIER_GPU);
+    const bool fused = kernel_addressable(src) && kernel_addressable(dst) && (!dst2 || kernel_addressable(*dst2)) &&
+                       ((src.tier == TIER_GPU && dst.tier == TIER_GPU && (!dst2 || dst2->tier == TIER_GPU)) ||
+                        (dst2 && gpu_dst));
+    if (fused) {
+        *used_stream = true;
+        err = cuda_err(ocmk::launch_copy((char *)dst.ptr + dst_off, dst2 ? (char *)dst2->ptr + dst2_off : nullptr,
+                                         (const char *)src.ptr + src_off, bytes, signal, next_ticket(), st, nullptr,
+                                         &c.kernel_launches),
+                       "copy kernel");
+        signalled = signal != nullptr;
+    } else {
+        err = single_copy(dst, dst_off, src, src_off, bytes, st, used_stream, dst2 ? nullptr : signal, &signalled);
+        if (!err && dst2)
+            err = single_copy(*dst2, dst2_off, dst, dst_off, bytes, st, used_stream, signal, &signalled);
+    }
+    if (!err && signal && !signalled) {
+        if (*used_stream) {
+            err = cuda_err(ocmk::launch_signal(signal, st), "signal kernel");
+            ++c.kernel_launches;
+        } else {
+            signal_rec->signal.fetch_add(1, std::memory_order_release);
+        }
+    }
+    return err;
+}
+
+static bool valid(ocm_alloc_t a) { return a && a->magic == kAllocMagic; }
+
+// The far side of a pair (single slab kinds only).
+static const Side *far_side(ocm_alloc_t a) { return (a->paired && a->remote.valid()) ? &a->remote : nullptr; }
+
+static void mark_pending(ocm_alloc_t a, void *stream, bool used) {
+    if (used && !stream) a->lib_stream_pending.store(true, std::memory_order_relaxed);
+}
+
+static int do_copy(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p, void *stream, bool *used) {
+    if (!valid(dst) || !valid(src) || !p) return OCM_EINVAL;
+    if (!p->op_flag) std::swap(dst, src);   // "read": data flows the other way (src/lib.c:510-515)
+    if (!dst->stripes.empty() || !src->stripes.empty()) return OCM_EUNSUPPORTED;
+    const Side *dfar = far_side(dst), *sfar = far_side(src);
+    const uint64_t n = p->bytes;
+    int err;
+    if (!dfar && !sfar) {
+        // local -> local (host/GPU in any combination; GPU->GPU is a no-op in the reference)
+        err = side_copy(dst->local, p->dest_offset, nullptr, 0, src->local, p->src_offset, n, dst->local.rec, stream, used);
+    } else if (dfar && !sfar) {
+        // local -> pair: hop 1 into the window, hop 2 window -> far side
+        if (!dst->local.valid()) {
+            err = side_copy(*dfar, p->dest_offset_2, nullptr, 0, src->local, p->src_offset, n, dfar->rec, stream, used);
+        } else if (p->src_offset_2 == p->dest_offset) {
+            err = side_copy(*dfar, p->dest_offset_2, &dst->local, p->dest_offset, src->local, p->src_offset, n,
+                            dfar->rec, stream, used);
+        } else {
+            err = side_copy(dst->local, p->dest_offset, nullptr, 0, src->local, p->src_offset, n, nullptr, stream, used);
+            if (!err)
+                err = side_copy(*dfar, p->dest_offset_2, nullptr, 0, dst->local, p->src_offset_2, n, dfar->rec, stream, used);
+        }
+    } else if (!dfar && sfar) {
+        // pair -> local: hop 1 far side -> window, hop 2 window -> destination
+        if (!src->local.valid()) {
+            err = side_copy(dst->local, p->dest_offset_2, nullptr, 0, *sfar, p->dest_offset, n, dst->local.rec, stream, used);
+        } else if (p->src_offset_2 == p->src_offset) {
+            err = side_copy(dst->local, p->dest_offset_2, &src->local, p->src_offset, *sfar, p->dest_offset, n,
+                            dst->local.rec, stream, used);
+        } else {
+            err = side_copy(src->local, p->src_offset, nullptr, 0, *sfar, p->dest_offset, n, nullptr, stream, used);
+            if (!err)
+                err = side_copy(dst->local, p->dest_offset_2, nullptr, 0, src->local, p->src_offset_2, n, dst->local.rec,
+                                stream, used);
+        }
+    } else {
+        // pair -> pair: third-party copy far side -> far side (BUG(1) in the reference, src/lib.c:591-594)
+        err = side_copy(*dfar, p->dest_offset, nullptr, 0, *sfar, p->src_offset, n, dfar->rec, stream, used);
+    }
+    mark_pending(dst, stream, *used);
+    mark_pending(src, stream, *used);
+    return err;
+}
+
+static int do_onesided(ocm_alloc_t a, const struct ocm_params *p, void *stream, bool *used) {
+    if (!valid(a) || !p) return OCM_EINVAL;
+    const Side *far = far_side(a);
+    if (!far || !a->local.valid()) {
+        LOGW("one-sided copy needs a paired allocation with a window");
+        return OCM_EINVAL;
+    }
+    if (p->bytes > a->local.bytes) return OCM_ERANGE;   // as the reference (src/lib.c:679,701)
+    int err;
+    if (p->op_flag) err = side_copy(*far, p->dest_offset, nullptr, 0, a->local, p->src_offset, p->bytes, far->rec, stream, used);
+    else err = side_copy(a->local, p->src_offset, nullptr, 0, *far, p->dest_offset, p->bytes, nullptr, stream, used);
+    mark_pending(a, stream, *used);
+    return err;
+}
+
+static int finish_sync(int err, bool used, void *stream) {
+    Ctx &c = ctx();
+    if (used && c.device >= 0) {
+        DeviceGuard dg(c.device);
+        cudaError_t e = cudaStreamSynchronize((cudaStream_t)(stream ? stream : c.stream));
+        if (e != cudaSuccess && !err) err = cuda_err(e, "stream sync");
+    }
+    set_last_error(err);
+    return err ? -1 : 0;
+}
+
+// Raw user pointer -> temporary side.
+static Side user_side(void *p, uint64_t bytes) {
+    Side s;
+    s.backing = SIDE_USER;
+    s.ptr = p;
+    s.bytes = bytes;
+    s.tier = TIER_HOST;
+    if (ctx().device >= 0) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, p) == cudaSuccess) {
+            if (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged) s.tier = TIER_GPU;
+        } else {
+            cudaGetLastError();
+        }
+    }
+    return s;
+}
+
+} // namespace ocm
+
+extern "C" {
+
+int ocm_copy_async(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p, void *stream) {
+    bool used = false;
+    int err = do_copy(dst, src, p, stream, &used);
+    set_last_error(err);
+    return -err;
+}
+
+int ocm_copy(ocm_alloc_t dst, ocm_alloc_t src, ocm_param_t p) {
+    bool used = false;
+    int err = do_copy(dst, src, p, nullptr, &used);
+    return finish_sync(err, used, nullptr);
+}
+
+int ocm_copy_onesided_async(ocm_alloc_t a, const struct ocm_params *p, void *stream) {
+    bool used = false;
+    int err = do_onesided(a, p, stream, &used);
+    set_last_error(err);
+    return -err;
+}
+
+int ocm_copy_onesided(ocm_alloc_t a, ocm_param_t p) {
+    bool used = false;
+    int err = do_onesided(a, p, nullptr, &used);
+    return finish_sync(err, used, nullptr);
+}
+
+int ocm_quiet(void) {
+    Ctx &c = ctx();
+    if (c.device < 0 || !c.stream) return 0;
+    DeviceGuard dg(c.device);
+    return cudaStreamSynchronize((cudaStream_t)c.stream) == cudaSuccess ? 0 : -OCM_ECUDA;
+}
+
+int ocm_copy_in(ocm_alloc_t dst, void *src) {
+    if (!valid(dst) || !src || !dst->stripes.empty()) {
+        set_last_error(OCM_EINVAL);
+        return -1;
+    }
+    bool used = false;
+    int err;
+    const Side *far = far_side(dst);
+    if (!far) {
+        Side u = user_side(src, dst->local.bytes);
+        err = side_copy(dst->local, 0, nullptr, 0, u, 0, dst->local.bytes, dst->local.rec, nullptr, &used);
+    } else if (!dst->local.valid()) {
+        Side u = user_side(src, far->bytes);
+        err = side_copy(*far, 0, nullptr, 0, u, 0, far->bytes, far->rec, nullptr, &used);
+    } else {
+        uint64_t n = std::min(dst->local.bytes, far->bytes);
+        Side u = user_side(src, n);
+        // window first, then window -> far side (the user pointer may be pageable host memory)
+        err = side_copy(dst->local, 0, nullptr, 0, u, 0, n, nullptr, nullptr, &used);
+        if (!err) err = side_copy(*far, 0, nullptr, 0, dst->local, 0, n, far->rec, nullptr, &used);
+    }
+    return finish_sync(err, used, nullptr);
+}
+
+int ocm_copy_out(void *dstp, ocm_alloc_t src) {
+    if (!valid(src) || !dstp || !src->stripes.empty()) {
+        set_last_error(OCM_EINVAL);
+        return -1;
+    }
+    bool used = false;
+    int err;
+    const Side *far = far_side(src);
+    if (!far) {
+        Side u = user_side(dstp, src->local.bytes);
+        err = side_copy(u, 0, nullptr, 0, src->local, 0, src->local.bytes, nullptr, nullptr, &used);
+    } else if (!src->local.valid()) {
+        Side u = user_side(dstp, far->bytes);
+        err = side_copy(u, 0, nullptr, 0, *far, 0, far->bytes, nullptr, nullptr, &used);
+    } else {
+        uint64_t n = std::min(src->local.bytes, far->bytes);
+        Side u = user_side(dstp, n);
+        err = side_copy(src->local, 0, nullptr, 0, *far, 0, n, nullptr, nullptr, &used);
+        if (!err) err = side_copy(u, 0, nullptr, 0, src->local, 0, n, nullptr, nullptr, &used);
+    }
+    return finish_sync(err, used, nullptr);
+}
+
+} // extern "C"

@@ -1,0 +1,107 @@
+// Internal state of libocm: daemon attachment, per-rank mapping cache,
+// allocation records.  Counterpart of the globals in reference src/lib.c:36-91.
+#pragma once
+#include "../common/gpu_rt.hpp"
+#include "../common/msg.hpp"
+#include "../common/tables.hpp"
+#include "../ipc/pmsg.hpp"
+#include "../../include/oncillamem.h"
+#include <atomic>
+#include <mutex>
+#include <unordered_set>
+#include <vector>
+
+namespace ocm {
+
+constexpr uint32_t kAllocMagic = 0x0C3A110Cu;
+
+// Everything this process knows about one rank: its tables and pools mapped
+// into our address space.  Filled lazily, kept until ocm_tini ("mapping cache":
+// after the first touch a remote region is plain pointer arithmetic).
+struct RankView {
+    bool         tried = false, ok = false;
+    ShmMapping   tbl_map;
+    TableHeader *hdr = nullptr;
+    ShmMapping   host_map;
+    bool         gpu_tried = false;
+    gpu::PoolMapping gpu;       // ptr == nullptr if the rank has no HBM pool or we have no GPU
+};
+
+enum SideBacking : uint8_t { SIDE_NONE = 0, SIDE_POOL = 1, SIDE_HEAP = 2, SIDE_CUDAMALLOC = 3, SIDE_USER = 4 };
+
+// One contiguous piece of memory addressable from this process.
+struct Side {
+    SideBacking backing = SIDE_NONE;
+    uint8_t     tier = TIER_HOST;
+    bool        via_daemon = false;   // allocated through the message protocol
+    int         rank = -1;            // owner rank (pool backing)
+    uint32_t    region = 0;
+    uint32_t    generation = 0;
+    uint64_t    id = 0;
+    uint64_t    offset = 0;
+    uint64_t    bytes = 0;            // usable (requested) bytes
+    void       *ptr = nullptr;
+    Region     *rec = nullptr;        // table record (signal word lives here)
+    bool valid() const { return backing != SIDE_NONE; }
+};
+
+} // namespace ocm
+
+// The opaque handle of the public API.
+struct lib_alloc {
+    uint32_t      magic;
+    enum ocm_kind kind;          // granted kind
+    bool          paired;
+    ocm::Side     local;         // local kinds: the memory; pairs: the window
+    ocm::Side     remote;        // pairs: the far side
+    std::vector<ocm::Side> stripes;   // striped / replicated kinds: one per rank
+    uint64_t      stripe_bytes;
+    std::atomic<bool> lib_stream_pending;
+};
+
+namespace ocm {
+
+struct Ctx {
+    std::mutex   mu;             // init/tini + allocation set
+    std::mutex   mq_mu;          // one request/reply exchange at a time
+    bool         inited = false;
+    int          rank = 0, n_ranks = 1;
+    int          daemon_pid = -1;
+    int          device = -1;    // CUDA device of this process (-1: none)
+    bool         force_slow = false;
+    Mailbox      box;
+    std::string  daemon_mq;
+    uint32_t     seq = 0;
+    ShmMapping   cluster_map;
+    ClusterTable *cluster = nullptr;
+    RankView     view[kMaxRanks];
+    std::unordered_set<lib_alloc *> allocs;
+    void        *stream = nullptr;      // library copy stream
+    unsigned    *tickets = nullptr;     // device-local election words
+    std::atomic<uint32_t> ticket_cursor{0};
+    // counters
+    std::atomic<uint64_t> n_alloc{0}, n_free{0}, n_fast{0}, n_slow{0}, n_copies{0}, copy_bytes{0};
+    unsigned long long kernel_launches = 0;
+    std::atomic<uint64_t> bytes_live[TIER_COUNT];
+};
+constexpr int kNumTickets = 1024;
+
+Ctx &ctx();
+void set_last_error(int e);
+// Map (once) the tables and host pool of `rank`; with_gpu also maps its HBM pool.
+RankView *get_view(int rank, bool with_gpu);
+// Exchange one message with the local daemon.  0 or positive ocm_err.
+int daemon_call(Message &m, int timeout_ms = 10000);
+unsigned *next_ticket();
+
+// copy engine (copy.cpp)
+int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2_off, const Side &src, uint64_t src_off,
+              uint64_t bytes, Region *signal_rec, void *stream, bool *used_stream);
+struct DeviceGuard {
+    int prev = -1;
+    bool switched = false;
+    explicit DeviceGuard(int dev);
+    ~DeviceGuard();
+};
+
+} // namespace ocm

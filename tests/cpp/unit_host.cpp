@@ -1,0 +1,492 @@
+// Native unit tests of the host substrate (no daemon, no GPU needed):
+//   unit_host <suite>|all     suites: msg nodefile ring tables tables_mt governor pmsg sock oracle
+// The reference has no unit layer at all; these are new.
+#include "common/governor.hpp"
+#include "common/msg.hpp"
+#include "common/names.hpp"
+#include "common/nodefile.hpp"
+#include "common/ring.hpp"
+#include "common/tables.hpp"
+#include "ipc/pmsg.hpp"
+#include "ipc/sock.hpp"
+#include "oracle/oracle.hpp"
+#include "../../include/oncillamem.h"
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <set>
+#include <string>
+#include <sys/socket.h>
+#include <sys/wait.h>
+#include <thread>
+#include <unistd.h>
+#include <vector>
+
+static int g_fail = 0;
+#define CHECK(cond)                                                                      \
+    do {                                                                                 \
+        if (!(cond)) {                                                                   \
+            fprintf(stderr, "FAIL %s:%d: %s\n", __FILE__, __LINE__, #cond);              \
+            ++g_fail;                                                                    \
+        }                                                                                \
+    } while (0)
+
+using namespace ocm;
+
+static void t_msg() {
+    Message m;
+    m.init(MSG_REQ_ALLOC);
+    CHECK(m.valid());
+    CHECK(sizeof(Message) == 192);
+    CHECK(m.type == MSG_REQ_ALLOC && m.status == MSG_REQUEST);
+    CHECK(MSG_CONNECT == 1 && MSG_RELEASE_APP == 9 && MSG_MAX == 11); // reference numbering, inc/msg.h:24-45
+    CHECK(!strcmp(msg_type_str(MSG_DO_FREE), "MSG_DO_FREE"));
+    CHECK(!strcmp(msg_status_str(MSG_RESPONSE), "MSG_RESPONSE"));
+    m.magic = 0;
+    CHECK(!m.valid());
+    CHECK(OCM_LOCAL_HOST == 1 && OCM_REMOTE_RDMA == 5 && OCM_LOCAL_GPU == 6 && OCM_REMOTE_GPU == 7);
+    CHECK(sizeof(struct ocm_params) == 48 && sizeof(struct ocm_alloc_params) == 24);
+}
+
+static void t_nodefile() {
+    Nodefile nf;
+    std::string err;
+    const char *ref = "#rank dns ethernet_ip ocm_port rdmacm_port\n"
+                      "0 shiva.cc.gt.atl.ga.us 143.215.131.65 12345 67890\n"
+                      "1 ifrit.cc.gt.atl.ga.us 143.215.131.185 12345 67890\n";
+    CHECK(parse_nodefile_text(ref, &nf, &err));
+    CHECK(nf.size() == 2 && nf.nodes[1].dns == "ifrit.cc.gt.atl.ga.us" && nf.nodes[1].ocm_port == 12345);
+    CHECK(nf.nodes[0].rdmacm_port == 67890);
+    CHECK(resolve_rank(nf, "ifrit.cc.gt.atl.ga.us", nullptr) == 1);
+    CHECK(resolve_rank(nf, "nobody", nullptr) == -1);
+    CHECK(resolve_rank(nf, "nobody", "1") == 1);
+    CHECK(resolve_rank(nf, "nobody", "7") == -1);
+    Nodefile rma;
+    CHECK(parse_nodefile_text("0 peac14 10.0.0.1 12345\n1 peac15 10.0.0.2 12345\n", &rma, &err)); // .rma variant
+    Nodefile ext;
+    CHECK(parse_nodefile_text("0 localhost 127.0.0.1 19000 0 gpu=0 gpu_bytes=2G host_bytes=256M\n"
+                              "1 localhost 127.0.0.1 19001 gpu=1 gpu_bytes=512M\n",
+                              &ext, &err));
+    CHECK(ext.nodes[0].gpu == 0 && ext.nodes[0].gpu_bytes == (2ull << 30) && ext.nodes[0].host_bytes == (256ull << 20));
+    CHECK(ext.nodes[1].gpu == 1 && ext.nodes[1].gpu_bytes == (512ull << 20));
+    CHECK(resolve_rank(ext, "localhost", nullptr) == 1); // highest rank first, as the reference
+    Nodefile one;
+    CHECK(parse_nodefile_text("0 whatever 127.0.0.1 19000\n", &one, &err));
+    CHECK(resolve_rank(one, "other", nullptr) == 0);
+    Nodefile bad;
+    CHECK(!parse_nodefile_text("0 a 1.2.3.4\n", &bad, &err));
+    CHECK(!parse_nodefile_text("0 a 1.2.3.4 1\n0 b 1.2.3.4 2\n", &bad, &err));
+    CHECK(!parse_nodefile_text("5 a 1.2.3.4 1\n", &bad, &err));
+    CHECK(!parse_nodefile_text("# only comments\n", &bad, &err));
+    CHECK(!parse_nodefile_text("0 a 1.2.3.4 1 bogus=3\n", &bad, &err));
+    uint64_t v;
+    CHECK(parse_size("4096", &v) && v == 4096);
+    CHECK(parse_size("1.5G", &v) && v == (3ull << 29));
+    CHECK(parse_size("64KiB", &v) && v == 65536);
+    CHECK(!parse_size("abc", &v));
+}
+
+static void t_ring() {
+    MpscRing<Message> q(8);
+    Message m;
+    CHECK(q.empty() && !q.pop(&m));
+    for (int i = 0; i < 8; ++i) {
+        m.init(MSG_PING);
+        m.seq = i;
+        CHECK(q.push(m));
+    }
+    CHECK(!q.push(m)); // full
+    for (int i = 0; i < 8; ++i) {
+        CHECK(q.pop(&m) && m.seq == (uint32_t)i);
+    }
+    CHECK(q.empty());
+    // many producers, one consumer, nothing lost or duplicated
+    MpscRing<uint64_t> r(256);
+    const int P = 4, N = 20000;
+    std::vector<std::thread> th;
+    for (int p = 0; p < P; ++p)
+        th.emplace_back([&, p] {
+            for (int i = 0; i < N; ++i) {
+                uint64_t v = ((uint64_t)p << 32) | (uint32_t)i;
+                while (!r.push(v)) std::this_thread::yield();
+            }
+        });
+    std::vector<int> next(P, 0);
+    int got = 0;
+    while (got < P * N) {
+        uint64_t v;
+        if (!r.pop(&v)) {
+            std::this_thread::yield();
+            continue;
+        }
+        int p = (int)(v >> 32), i = (int)(uint32_t)v;
+        CHECK(p < P && i == next[p]); // per-producer FIFO order
+        next[p] = i + 1;
+        ++got;
+    }
+    for (auto &t : th) t.join();
+    CHECK(r.empty());
+}
+
+static TableHeader *fresh_table(std::vector<char> &buf, uint64_t gpu, uint64_t host) {
+    size_t seg = table_segment_bytes(gpu, host);
+    buf.assign(seg, 0);
+    table_format(buf.data(), seg, 0, 1, 1234, gpu, host);
+    auto *h = reinterpret_cast<TableHeader *>(buf.data());
+    CHECK(table_validate(h, seg));
+    return h;
+}
+
+static void t_tables() {
+    // size classes: monotone, waste bounded by 25 %
+    uint32_t prev = 0;
+    for (int c = 0; c < kNumClasses && class_granules(c) != 0xFFFFFFFFu; ++c) {
+        CHECK(class_granules(c) > prev);
+        prev = class_granules(c);
+    }
+    for (uint64_t g : {1ull, 2ull, 7ull, 9ull, 17ull, 100ull, 1000ull, 65537ull, 1000000ull}) {
+        int c = class_of(g);
+        CHECK(c >= 0 && class_granules(c) >= g);
+        CHECK((double)class_granules(c) <= 1.25 * (double)g + 1.0);
+        CHECK(c == 0 || class_granules(c - 1) < g);
+    }
+    std::vector<char> buf;
+    TableHeader *h = fresh_table(buf, 64ull << 20, 1ull << 20); // 1024 GPU granules of 64 KiB, 256 host granules
+    CHECK(h->pool[TIER_GPU].granule == 65536 && h->pool[TIER_GPU].n_granules == 1024);
+    CHECK(h->pool[TIER_HOST].granule == 4096 && h->pool[TIER_HOST].n_granules == 256);
+    BlockRef a, b, c;
+    CHECK(pool_alloc(h, TIER_GPU, 100, 11, 0, &a) == OCM_OK && a.offset == 0 && a.block_bytes == 65536);
+    CHECK(pool_alloc(h, TIER_GPU, 65537, 11, 0, &b) == OCM_OK && b.offset == 65536 && b.block_bytes == 131072);
+    CHECK(a.id != b.id);
+    CHECK(h->pool[TIER_GPU].used_bytes.load() == 3 * 65536 && h->pool[TIER_GPU].live.load() == 2);
+    Region *regs = table_regions(h, TIER_GPU);
+    CHECK(regs[a.region].state.load() == REGION_LIVE && regs[a.region].owner_pid == 11 && regs[a.region].bytes == 100);
+    // free -> dirty -> scrub -> reuse
+    CHECK(pool_free(h, TIER_GPU, a.region, a.id) == OCM_OK);
+    CHECK(pool_free(h, TIER_GPU, a.region, a.id) == OCM_ESTALE);       // double free
+    CHECK(pool_free(h, TIER_GPU, b.region, b.id + 77) == OCM_ESTALE);   // wrong id
+    CHECK(regs[a.region].state.load() == REGION_DIRTY);
+    CHECK(pool_alloc(h, TIER_GPU, 100, 12, 0, &c) == OCM_OK && c.offset != a.offset); // dirty block not reused yet
+    std::vector<DirtyBlock> dirty;
+    CHECK(pool_take_dirty(h, TIER_GPU, &dirty) == 1 && dirty[0].region == a.region && dirty[0].bytes == 65536);
+    CHECK(regs[a.region].state.load() == REGION_SCRUBBING);
+    pool_release_scrubbed(h, TIER_GPU, a.region);
+    BlockRef d;
+    CHECK(pool_alloc(h, TIER_GPU, 4096, 13, 0, &d) == OCM_OK && d.offset == a.offset && d.generation == a.generation + 1);
+    // exhaustion and capacity accounting
+    BlockRef big;
+    CHECK(pool_alloc(h, TIER_GPU, 128ull << 20, 1, 0, &big) == OCM_ENOMEM);
+    std::vector<BlockRef> many;
+    for (;;) {
+        BlockRef x;
+        if (pool_alloc(h, TIER_GPU, 65536, 14, 0, &x) != OCM_OK) break;
+        many.push_back(x);
+    }
+    CHECK(many.size() == 1024 - 4);
+    CHECK(pool_count_live(h, TIER_GPU) == many.size() + 3);
+    // without scrubbing blocks are reusable at once; a bigger free block serves a smaller request
+    h->scrub_enabled.store(0);
+    CHECK(pool_free(h, TIER_GPU, b.region, b.id) == OCM_OK);
+    BlockRef e;
+    CHECK(pool_alloc(h, TIER_GPU, 10, 15, 0, &e) == OCM_OK && e.offset == b.offset && e.block_bytes == 131072);
+    // reclaim by owner
+    uint64_t bytes = 0;
+    auto pred = [](int pid, int, void *) { return pid == 14; };
+    CHECK(pool_reclaim(h, TIER_GPU, pred, nullptr, &bytes) == many.size());
+    CHECK(bytes == many.size() * 65536ull);
+    CHECK(pool_count_live(h, TIER_GPU) == 3);
+    // host tier independent
+    BlockRef hb;
+    CHECK(pool_alloc(h, TIER_HOST, 5000, 1, 0, &hb) == OCM_OK && hb.block_bytes == 8192);
+    CHECK(pool_alloc(h, 7, 1, 1, 0, &hb) == OCM_EINVAL);
+}
+
+static void t_tables_mt() {
+    // concurrent alloc/free from several threads: no block handed out twice
+    std::vector<char> buf;
+    TableHeader *h = fresh_table(buf, 256ull << 20, 0);
+    h->scrub_enabled.store(0);
+    const int T = 8, ITER = 20000;
+    std::vector<std::atomic<int>> owner(h->pool[TIER_GPU].n_granules);
+    for (auto &o : owner) o.store(0);
+    std::atomic<int> errors{0};
+    std::vector<std::thread> th;
+    for (int t = 0; t < T; ++t)
+        th.emplace_back([&, t] {
+            std::vector<BlockRef> mine;
+            uint64_t rng = 88172645463325252ull + t;
+            for (int i = 0; i < ITER; ++i) {
+                rng ^= rng << 13; rng ^= rng >> 7; rng ^= rng << 17;
+                if (mine.size() < 16 && (rng & 1)) {
+                    BlockRef b;
+                    uint64_t sz = ((rng >> 8) % 6 + 1) * 65536;
+                    if (pool_alloc(h, TIER_GPU, sz, 100 + t, 0, &b) == OCM_OK) {
+                        uint32_t g = (uint32_t)(b.block_bytes / 65536);
+                        for (uint32_t k = 0; k < g; ++k)
+                            if (owner[b.region + k].exchange(t + 1) != 0) errors++;
+                        mine.push_back(b);
+                    }
+                } else if (!mine.empty()) {
+                    BlockRef b = mine.back();
+                    mine.pop_back();
+                    uint32_t g = (uint32_t)(b.block_bytes / 65536);
+                    for (uint32_t k = 0; k < g; ++k)
+                        if (owner[b.region + k].exchange(0) != t + 1) errors++;
+                    if (pool_free(h, TIER_GPU, b.region, b.id) != OCM_OK) errors++;
+                }
+            }
+            for (auto &b : mine) {
+                uint32_t g = (uint32_t)(b.block_bytes / 65536);
+                for (uint32_t k = 0; k < g; ++k) owner[b.region + k].store(0);
+                if (pool_free(h, TIER_GPU, b.region, b.id) != OCM_OK) errors++;
+            }
+        });
+    for (auto &t : th) t.join();
+    CHECK(errors.load() == 0);
+    CHECK(h->pool[TIER_GPU].live.load() == 0 && h->pool[TIER_GPU].used_bytes.load() == 0);
+    CHECK(h->pool[TIER_GPU].total_allocs.load() == h->pool[TIER_GPU].total_frees.load());
+    CHECK(pool_count_live(h, TIER_GPU) == 0);
+}
+
+static void t_governor() {
+    std::vector<char> buf(sizeof(ClusterTable), 0);
+    auto *c = reinterpret_cast<ClusterTable *>(buf.data());
+    cluster_format(c, 4);
+    NodeConfig cfg;
+    memset(&cfg, 0, sizeof cfg);
+    uint64_t pools[TIER_COUNT] = {1ull << 30, 1ull << 28};
+    for (int r = 0; r < 3; ++r) { // rank 3 never joins
+        cfg.gpu_index = r;
+        CHECK(governor_add_node(c, r, cfg, pools) == OCM_OK);
+    }
+    CHECK(governor_joined(c) == 3);
+    AllocRequest rq;
+    memset(&rq, 0, sizeof rq);
+    Allocation a;
+    rq.orig_rank = 1; rq.bytes = 1 << 20; rq.type = ALLOC_MEM_REMOTE_GPU; rq.policy = OCM_POLICY_DEFAULT;
+    CHECK(governor_place(c, rq, &a) == OCM_OK && a.remote_rank == 2 && a.tier == TIER_GPU); // neighbour (r+1)%N
+    rq.orig_rank = 2;
+    CHECK(governor_place(c, rq, &a) == OCM_OK && a.remote_rank == 0); // rank 3 absent -> next neighbour
+    rq.type = ALLOC_MEM_HOST;
+    CHECK(governor_place(c, rq, &a) == OCM_OK && a.remote_rank == 2 && a.tier == TIER_HOST); // local kinds stay
+    rq.type = ALLOC_MEM_RDMA; rq.orig_rank = 0;
+    CHECK(governor_place(c, rq, &a) == OCM_OK && a.remote_rank == 1 && a.tier == TIER_HOST && a.type == ALLOC_MEM_RDMA);
+    rq.type = ALLOC_MEM_REMOTE_GPU; rq.policy = OCM_POLICY_EXPLICIT; rq.remote_rank = 2;
+    CHECK(governor_place(c, rq, &a) == OCM_OK && a.remote_rank == 2);
+    rq.remote_rank = 3;
+    CHECK(governor_place(c, rq, &a) == OCM_ENOMEM); // not joined
+    rq.remote_rank = 9;
+    CHECK(governor_place(c, rq, &a) == OCM_EINVAL);
+    // capacity: fill rank 1's GPU pool, then the request spills to the host tier of rank 1, then moves on
+    rq.policy = OCM_POLICY_EXPLICIT; rq.remote_rank = 1; rq.bytes = 1ull << 30;
+    CHECK(governor_place(c, rq, &a) == OCM_OK && a.tier == TIER_GPU);
+    rq.bytes = 1ull << 27;
+    CHECK(governor_place(c, rq, &a) == OCM_OK && a.tier == TIER_HOST && a.type == ALLOC_MEM_REMOTE_HOST);
+    governor_release(c, 1, TIER_GPU, 1ull << 30);
+    CHECK(governor_place(c, rq, &a) == OCM_OK && a.tier == TIER_GPU);
+    // least loaded picks the emptiest pool
+    rq.policy = OCM_POLICY_LEAST_LOADED; rq.orig_rank = 0; rq.bytes = 1 << 20;
+    uint64_t u0 = c->node[0].used[TIER_GPU].load(), u1 = c->node[1].used[TIER_GPU].load(), u2 = c->node[2].used[TIER_GPU].load();
+    CHECK(governor_place(c, rq, &a) == OCM_OK);
+    uint64_t mn = std::min(u0, std::min(u1, u2));
+    uint64_t chosen = a.remote_rank == 0 ? u0 : a.remote_rank == 1 ? u1 : u2;
+    CHECK(chosen == mn);
+    // round robin cycles over joined ranks
+    rq.policy = OCM_POLICY_ROUND_ROBIN;
+    std::set<int> seen;
+    for (int i = 0; i < 6; ++i) {
+        CHECK(governor_place(c, rq, &a) == OCM_OK);
+        seen.insert(a.remote_rank);
+    }
+    CHECK(seen.size() == 3);
+    // single-rank cluster keeps remote requests on rank 0 (the reference downgrades to host, src/alloc.c:82-83)
+    std::vector<char> b1(sizeof(ClusterTable), 0);
+    auto *c1 = reinterpret_cast<ClusterTable *>(b1.data());
+    cluster_format(c1, 1);
+    CHECK(governor_add_node(c1, 0, cfg, pools) == OCM_OK);
+    rq.policy = OCM_POLICY_DEFAULT; rq.orig_rank = 0;
+    CHECK(governor_place(c1, rq, &a) == OCM_OK && a.remote_rank == 0 && a.tier == TIER_GPU);
+}
+
+static void t_pmsg() {
+    // equivalent of the reference's pmsg_daemon / pmsg_client pair (test/pmsg_daemon.c, test/pmsg_client.c)
+    setenv("OCM_NS", ("ut" + std::to_string(getpid())).c_str(), 1);
+    struct Toy { int type; int pid; char text[256]; };
+    Mailbox daemon;
+    CHECK(daemon.open(mq_daemon_name(0), sizeof(Toy)) == 0);
+    CHECK(daemon.pending() == 0);
+    pid_t child = fork();
+    if (child == 0) {
+        Mailbox me;
+        if (me.open(mq_app_name(getpid()), sizeof(Toy))) _exit(10);
+        if (me.attach(mq_daemon_name(0))) _exit(11);
+        Toy t = {1, (int)getpid(), "hello"};
+        if (me.send(mq_daemon_name(0), &t)) _exit(12);
+        Toy r;
+        if (me.recv(&r, 5000) != 1) _exit(13);
+        if (strcmp(r.text, "nice to meet you")) _exit(14);
+        me.detach(mq_daemon_name(0));
+        me.close();
+        _exit(0);
+    }
+    Toy t;
+    CHECK(daemon.recv(&t, 5000) == 1);
+    CHECK(t.pid == child && !strcmp(t.text, "hello"));
+    CHECK(daemon.attach(mq_app_name(t.pid)) == 0);
+    Toy r = {2, (int)getpid(), "nice to meet you"};
+    CHECK(daemon.send(mq_app_name(t.pid), &r) == 0);
+    int st = 0;
+    waitpid(child, &st, 0);
+    CHECK(WIFEXITED(st) && WEXITSTATUS(st) == 0);
+    CHECK(daemon.detach(mq_app_name(t.pid)) == 0);
+    CHECK(daemon.recv(&t, 0) == 0);       // non-blocking poll, empty
+    CHECK(daemon.recv(&t, 20) == 0);      // timed wait, empty
+    CHECK(daemon.send("/ocm_mq_nobody", &r) == -ENOTCONN);
+    // a second owner of the same name steals a stale queue only when asked to
+    Mailbox dup;
+    CHECK(dup.open(mq_daemon_name(0), sizeof(Toy), 8, false) == -EEXIST);
+    // queue depth back-pressure: 8 messages fit, the 9th times out
+    Mailbox self;
+    CHECK(self.attach(mq_daemon_name(0)) == 0);
+    for (int i = 0; i < 8; ++i) CHECK(self.send(mq_daemon_name(0), &r, 0) == 0);
+    CHECK(self.send(mq_daemon_name(0), &r, 30) == -ETIMEDOUT);
+    CHECK(daemon.pending() == 8);
+    CHECK(daemon.close() == 0);
+    // C wrappers with the reference's signatures
+    setenv("OCM_RANK", "0", 1);
+    CHECK(pmsg_init(sizeof(Toy)) == 0);
+    CHECK(pmsg_open(PMSG_DAEMON_PID) == 0);
+    CHECK(pmsg_attach(PMSG_DAEMON_PID) == 0);
+    CHECK(pmsg_send(PMSG_DAEMON_PID, &r) == 0);
+    CHECK(pmsg_pending() == 1);
+    CHECK(pmsg_recv(&t, true) == 0 && t.type == 2);
+    CHECK(pmsg_recv(&t, false) != 0);
+    CHECK(pmsg_detach(PMSG_DAEMON_PID) == 0);
+    CHECK(pmsg_close() == 0);
+}
+
+static void t_sock() {
+    std::string name = "ocm_ut_" + std::to_string(getpid());
+    int l = uds_listen(name);
+    CHECK(l >= 0);
+    int pipefd[2];
+    CHECK(pipe(pipefd) == 0);
+    pid_t child = fork();
+    if (child == 0) {
+        int s = uds_connect(name, 1000);
+        if (s < 0) _exit(20);
+        uint64_t payload = 0;
+        int fd = -1;
+        if (uds_recv_fd(s, &payload, sizeof payload, &fd, 2000) != 1) _exit(21);
+        if (payload != 0xfeedfacecafebeefull || fd < 0) _exit(22);
+        const char msg[] = "through the passed fd";
+        if (write(fd, msg, sizeof msg) != (ssize_t)sizeof msg) _exit(23);
+        _exit(0);
+    }
+    int s = accept(l, nullptr, nullptr);
+    CHECK(s >= 0);
+    uint64_t payload = 0xfeedfacecafebeefull;
+    CHECK(uds_send_fd(s, &payload, sizeof payload, pipefd[1]) == 1);
+    char buf[64] = {0};
+    CHECK(read(pipefd[0], buf, sizeof buf) > 0 && !strcmp(buf, "through the passed fd"));
+    int st = 0;
+    waitpid(child, &st, 0);
+    CHECK(WIFEXITED(st) && WEXITSTATUS(st) == 0);
+    sock_close(s);
+    sock_close(l);
+    // TCP round trip of one wire message, 1/0/-errno tri-state
+    int port = 20000 + (getpid() % 20000);
+    int tl = tcp_listen("127.0.0.1", port);
+    CHECK(tl >= 0);
+    int cfd = tcp_connect("127.0.0.1", port, 1000);
+    CHECK(cfd >= 0);
+    int afd = tcp_accept(tl);
+    CHECK(afd >= 0);
+    Message m, r;
+    m.init(MSG_PING);
+    m.seq = 42;
+    CHECK(sock_put(cfd, &m, sizeof m) == 1);
+    CHECK(sock_get(afd, &r, sizeof r, 1000) == 1 && r.valid() && r.seq == 42);
+    CHECK(sock_get(afd, &r, sizeof r, 20) == -ETIMEDOUT);
+    sock_close(cfd);
+    CHECK(sock_get(afd, &r, sizeof r, 1000) == 0); // peer closed
+    sock_close(afd);
+    sock_close(tl);
+    CHECK(tcp_connect("127.0.0.1", port, 200) < 0);
+}
+
+static void t_oracle() {
+    // e4m3: every finite code point round-trips; rounding is to nearest even; saturation at 448
+    for (int v = 0; v < 256; ++v) {
+        if ((v & 0x7f) == 0x7f) continue;
+        float f = ocm_oracle_e4m3_to_f32((uint8_t)v);
+        uint8_t back = ocm_oracle_f32_to_e4m3(f);
+        CHECK(back == v || (f == 0.0f && (back & 0x7f) == 0));
+    }
+    CHECK(ocm_oracle_e4m3_to_f32(0x7e) == 448.0f && ocm_oracle_e4m3_to_f32(0x01) == ldexpf(1.0f, -9));
+    CHECK(ocm_oracle_f32_to_e4m3(1e9f) == 0x7e && ocm_oracle_f32_to_e4m3(-1e9f) == 0xfe);
+    CHECK(ocm_oracle_f32_to_e4m3(17.0f) == ocm_oracle_f32_to_e4m3(16.0f));   // tie -> even (16 | 18)
+    CHECK(ocm_oracle_f32_to_e4m3(19.0f) == ocm_oracle_f32_to_e4m3(20.0f));   // tie -> even (18 | 20)
+    CHECK(ocm_oracle_f32_to_e4m3(465.0f) == 0x7e);
+    CHECK(ocm_oracle_f32_to_bf16(1.0f) == 0x3f80 && ocm_oracle_bf16_to_f32(0x3f80) == 1.0f);
+    CHECK(ocm_oracle_f32_to_bf16(1.00390625f) == 0x3f80);                    // tie -> even
+    CHECK(ocm_oracle_f32_to_bf16(1.01171875f) == 0x3f82);                    // tie -> even (odd rounds up)
+    // fill / verify / checksum agree with each other
+    std::vector<uint8_t> b(1003);
+    ocm_oracle_fill(b.data(), b.size(), 0x0807060504030201ull);
+    CHECK(b[0] == 1 && b[7] == 8 && b[8] == 1 && b[1002] == (1002 % 8) + 1);
+    CHECK(ocm_oracle_verify(b.data(), b.size(), 0x0807060504030201ull) == 0);
+    b[500] ^= 0xff;
+    CHECK(ocm_oracle_verify(b.data(), b.size(), 0x0807060504030201ull) == 1);
+    uint64_t w[2] = {5, 7};
+    CHECK(ocm_oracle_checksum(w, 16) == 12 && ocm_oracle_checksum(w, 9) == 5 + 7);
+    // strided quantise -> dequantise stays within the e4m3 step (2^-3 relative, half of it after RNE)
+    const int R = 6, E = 96;
+    std::vector<float> src(R * 128), deq(R * E);
+    std::vector<uint8_t> q(R * E);
+    std::vector<float> sc(R * 3);
+    for (size_t i = 0; i < src.size(); ++i) src[i] = sinf((float)i * 0.37f) * (1.0f + (float)(i % 7));
+    ocm_oracle_strided d;
+    memset(&d, 0, sizeof d);
+    d.src = src.data(); d.dst = q.data(); d.row_bytes = E * 4; d.n[0] = R; d.n[1] = d.n[2] = 1;
+    d.src_stride[0] = 128 * 4; d.dst_stride[0] = E; d.src_dtype = 1; d.dst_dtype = 3; d.scale_block = 32; d.scales = sc.data();
+    CHECK(ocm_oracle_strided_copy(&d) == 0);
+    ocm_oracle_strided u = d;
+    u.src = q.data(); u.dst = deq.data(); u.row_bytes = E; u.src_stride[0] = E; u.dst_stride[0] = E * 4;
+    u.src_dtype = 3; u.dst_dtype = 1;
+    CHECK(ocm_oracle_strided_copy(&u) == 0);
+    for (int r = 0; r < R; ++r)
+        for (int e = 0; e < E; ++e) {
+            float x = src[r * 128 + e], y = deq[r * E + e], s = sc[r * 3 + e / 32];
+            CHECK(fabsf(x - y) <= 0.0625f * fabsf(x) + s * ldexpf(1.0f, -10) + 1e-12f);
+        }
+    // GUPS is an involution: applying the same stream twice restores the table
+    std::vector<uint64_t> tab(1 << 10, 3);
+    ocm_oracle_gups(tab.data(), tab.size(), 5000, 99, 128);
+    bool changed = false;
+    for (auto x : tab) changed |= x != 3;
+    CHECK(changed);
+    ocm_oracle_gups(tab.data(), tab.size(), 5000, 99, 128);
+    for (auto x : tab) CHECK(x == 3);
+}
+
+int main(int argc, char **argv) {
+    std::string which = argc > 1 ? argv[1] : "all";
+    std::map<std::string, void (*)()> suites = {
+        {"msg", t_msg}, {"nodefile", t_nodefile}, {"ring", t_ring}, {"tables", t_tables}, {"tables_mt", t_tables_mt},
+        {"governor", t_governor}, {"pmsg", t_pmsg}, {"sock", t_sock}, {"oracle", t_oracle}};
+    int ran = 0;
+    for (auto &kv : suites) {
+        if (which != "all" && which != kv.first) continue;
+        int before = g_fail;
+        kv.second();
+        printf("%s: %s\n", kv.first.c_str(), g_fail == before ? "pass" : "FAIL");
+        ++ran;
+    }
+    if (!ran) {
+        fprintf(stderr, "unknown suite %s\n", which.c_str());
+        return 2;
+    }
+    return g_fail ? 1 : 0;
+}
