@@ -1,0 +1,144 @@
+"""Launch and manage a set of ``oncillamem`` daemons on this host.
+
+The reference needs one real machine per rank (rank = hostname match, one global
+daemon queue per host: reference src/nodefile.c:92-103, inc/pmsg.h:24) and refers
+to a ``bin/launch`` script that does not exist (reference README:42-43).  Here N
+ranks (one per GPU) run on one box: ``OCM_RANK`` picks the rank and ``OCM_NS``
+isolates the IPC names of concurrent clusters.
+"""
+from __future__ import annotations
+
+import os
+import signal
+import socket
+import subprocess
+import tempfile
+import time
+from pathlib import Path
+
+from . import _native
+
+
+def _free_ports(n: int) -> list[int]:
+    socks, ports = [], []
+    for _ in range(n):
+        s = socket.socket()
+        s.bind(("127.0.0.1", 0))
+        socks.append(s)
+        ports.append(s.getsockname()[1])
+    for s in socks:
+        s.close()
+    return ports
+
+
+def write_nodefile(path: str | Path, n_ranks: int, ports: list[int] | None = None, gpus: list[int] | None = None,
+                   gpu_bytes: int | None = None, host_bytes: int | None = None, hostname: str = "localhost") -> list[int]:
+    ports = ports or _free_ports(n_ranks)
+    lines = ["#rank dns ethernet_ip ocm_port rdmacm_port [gpu=<i> gpu_bytes=<n> host_bytes=<n>]"]
+    for r in range(n_ranks):
+        opts = []
+        if gpus is not None:
+            opts.append(f"gpu={gpus[r]}")
+        if gpu_bytes is not None:
+            opts.append(f"gpu_bytes={int(gpu_bytes)}")
+        if host_bytes is not None:
+            opts.append(f"host_bytes={int(host_bytes)}")
+        lines.append(f"{r} {hostname} 127.0.0.1 {ports[r]} 0 " + " ".join(opts))
+    Path(path).write_text("\n".join(lines) + "\n")
+    return ports
+
+
+class LocalCluster:
+    """N daemons on this host.  Use as a context manager.
+
+    ``ranks`` restricts which ranks THIS process starts (a torchrun rank starts only its own daemon
+    and shares the nodefile with its peers through ``nodefile=``).
+    """
+
+    def __init__(self, n_ranks: int = 1, *, gpus: list[int] | None | str = "auto", gpu_bytes: int | None = None,
+                 host_bytes: int | None = 64 << 20, ns: str | None = None, nodefile: str | None = None,
+                 ranks: list[int] | None = None, log_level: str | None = None, extra_env: dict | None = None,
+                 ports: list[int] | None = None):
+        self.n_ranks = n_ranks
+        self.ns = ns if ns is not None else f"c{os.getpid()}"
+        self.ranks = list(range(n_ranks)) if ranks is None else list(ranks)
+        self.procs: dict[int, subprocess.Popen] = {}
+        self._tmp = None
+        self.log_level = log_level or os.environ.get("OCM_LOG", "warn")
+        self.extra_env = dict(extra_env or {})
+        if gpus == "auto":
+            gpus = None  # daemon picks rank % device_count (or none without a GPU)
+        self.gpus = gpus
+        if nodefile is None:
+            self._tmp = tempfile.TemporaryDirectory(prefix="ocm_")
+            nodefile = os.path.join(self._tmp.name, "nodefile")
+            write_nodefile(nodefile, n_ranks, ports=ports, gpus=gpus, gpu_bytes=gpu_bytes, host_bytes=host_bytes)
+        self.nodefile = nodefile
+        self.logs: dict[int, str] = {}
+
+    def env(self, rank: int = 0) -> dict:
+        e = dict(os.environ)
+        e.update(self.extra_env)
+        e["OCM_NS"] = self.ns
+        e["OCM_RANK"] = str(rank)
+        e["OCM_LOG"] = self.log_level
+        return e
+
+    def apply_env(self, rank: int = 0) -> None:
+        """Point THIS process at ``rank``'s daemon (call before ``ocm.init()``)."""
+        os.environ["OCM_NS"] = self.ns
+        os.environ["OCM_RANK"] = str(rank)
+
+    def start(self, timeout: float = 60.0) -> "LocalCluster":
+        logdir = self._tmp.name if self._tmp else tempfile.mkdtemp(prefix="ocm_logs_")
+        for r in sorted(self.ranks):   # rank 0 (the master) first
+            log = os.path.join(logdir, f"daemon{r}.log")
+            self.logs[r] = log
+            with open(log, "w") as f:
+                self.procs[r] = subprocess.Popen([str(_native.DAEMON_PATH), self.nodefile], env=self.env(r), stdout=f,
+                                                 stderr=subprocess.STDOUT, start_new_session=True)
+            self._wait_ready(r, timeout)
+        return self
+
+    def _wait_ready(self, r: int, timeout: float) -> None:
+        t0 = time.time()
+        while time.time() - t0 < timeout:
+            if self.procs[r].poll() is not None:
+                raise RuntimeError(f"daemon {r} exited with {self.procs[r].returncode}:\n{self.read_log(r)}")
+            if "oncillamem ready" in self.read_log(r):
+                return
+            time.sleep(0.01)
+        raise TimeoutError(f"daemon {r} not ready after {timeout}s:\n{self.read_log(r)}")
+
+    def read_log(self, r: int) -> str:
+        try:
+            return Path(self.logs[r]).read_text(errors="replace")
+        except OSError:
+            return ""
+
+    def kill(self, rank: int, sig: int = signal.SIGKILL) -> None:
+        p = self.procs.get(rank)
+        if p and p.poll() is None:
+            p.send_signal(sig)
+            p.wait(timeout=10)
+
+    def stop(self) -> None:
+        for r, p in self.procs.items():
+            if p.poll() is None:
+                p.send_signal(signal.SIGTERM)
+        for r, p in self.procs.items():
+            try:
+                p.wait(timeout=10)
+            except subprocess.TimeoutExpired:
+                p.kill()
+                p.wait()
+        self.procs.clear()
+        if self._tmp:
+            self._tmp.cleanup()
+            self._tmp = None
+
+    def __enter__(self) -> "LocalCluster":
+        return self.start()
+
+    def __exit__(self, *exc) -> None:
+        self.stop()

@@ -10,32 +10,7 @@
 
 namespace ocm {
 
-// ---------------------------------------------------------------- classes --
 namespace {
-struct ClassTable {
-    uint32_t g[kNumClasses];
-    int n;
-    ClassTable() {
-        n = 0;
-        for (uint32_t s = 1; s <= 8; ++s) g[n++] = s;
-        // four steps per doubling: 10 12 14 16 | 20 24 28 32 | ...
-        for (uint64_t base = 8; n < kNumClasses;) {
-            uint64_t step = base / 4;
-            for (int i = 1; i <= 4 && n < kNumClasses; ++i) {
-                uint64_t v = base + step * i;
-                if (v > 0xFFFFFFFFull) { g[n++] = 0xFFFFFFFFu; continue; }
-                g[n++] = (uint32_t)v;
-            }
-            base *= 2;
-            if (base > (1ull << 33)) break;
-        }
-        for (; n < kNumClasses; ++n) g[n] = 0xFFFFFFFFu;
-    }
-};
-const ClassTable &classes() {
-    static ClassTable t;
-    return t;
-}
 inline uint64_t pack_head(uint32_t tag, uint32_t idx_plus1) { return ((uint64_t)tag << 32) | idx_plus1; }
 inline uint32_t head_idx(uint64_t h) { return (uint32_t)h; }
 inline uint32_t head_tag(uint64_t h) { return (uint32_t)(h >> 32); }
@@ -48,30 +23,91 @@ void stack_push(std::atomic<uint64_t> &head, Region *regs, uint32_t idx) {
         if (head.compare_exchange_weak(h, nh, std::memory_order_acq_rel, std::memory_order_acquire)) return;
     }
 }
-// returns idx+1 or 0
-uint32_t stack_pop(std::atomic<uint64_t> &head, Region *regs) {
-    uint64_t h = head.load(std::memory_order_acquire);
-    for (;;) {
-        uint32_t ip1 = head_idx(h);
-        if (!ip1) return 0;
-        uint32_t nxt = regs[ip1 - 1].next.load(std::memory_order_relaxed);
-        uint64_t nh = pack_head(head_tag(h) + 1, nxt);
-        if (head.compare_exchange_weak(h, nh, std::memory_order_acq_rel, std::memory_order_acquire)) return ip1;
+
+// mask of bits [lo, hi) inside one 64-bit word (0 <= lo < hi <= 64)
+inline uint64_t bits(unsigned lo, unsigned hi) {
+    uint64_t m = hi >= 64 ? ~0ull : ((1ull << hi) - 1);
+    return m & ~((1ull << lo) - 1);
+}
+
+void bitmap_clear(std::atomic<uint64_t> *bm, uint64_t start, uint64_t n) {
+    uint64_t i = start, end = start + n;
+    while (i < end) {
+        uint64_t w = i >> 6;
+        unsigned lo = (unsigned)(i & 63);
+        unsigned hi = (unsigned)std::min<uint64_t>(64, lo + (end - i));
+        bm[w].fetch_and(~bits(lo, hi), std::memory_order_release);
+        i += hi - lo;
     }
 }
-} // namespace
 
-uint32_t class_granules(int cls) { return (cls >= 0 && cls < kNumClasses) ? classes().g[cls] : 0; }
-
-int class_of(uint64_t granules) {
-    if (granules == 0) granules = 1;
-    const uint32_t *g = classes().g;
-    const uint32_t *e = g + kNumClasses;
-    if (granules > 0xFFFFFFFEull) return -1;
-    const uint32_t *p = std::lower_bound(g, e, (uint32_t)granules);
-    if (p == e || *p == 0xFFFFFFFFu) return -1;
-    return (int)(p - g);
+// Try to take [start, start+n).  On conflict everything taken so far is given
+// back and *conflict receives the first granule found busy.
+bool bitmap_claim(std::atomic<uint64_t> *bm, uint64_t start, uint64_t n, uint64_t *conflict) {
+    uint64_t i = start, end = start + n;
+    while (i < end) {
+        uint64_t w = i >> 6;
+        unsigned lo = (unsigned)(i & 63);
+        unsigned hi = (unsigned)std::min<uint64_t>(64, lo + (end - i));
+        uint64_t m = bits(lo, hi);
+        uint64_t old = bm[w].load(std::memory_order_relaxed);
+        for (;;) {
+            if (old & m) {
+                if (i > start) bitmap_clear(bm, start, i - start);
+                *conflict = (w << 6) + (unsigned)__builtin_ctzll(old & m);
+                return false;
+            }
+            if (bm[w].compare_exchange_weak(old, old | m, std::memory_order_acq_rel, std::memory_order_relaxed)) break;
+        }
+        i += hi - lo;
+    }
+    return true;
 }
+
+// First granule >= from that is free, or N.
+uint64_t next_free(std::atomic<uint64_t> *bm, uint64_t from, uint64_t N) {
+    uint64_t i = from;
+    while (i < N) {
+        uint64_t w = i >> 6;
+        uint64_t word = bm[w].load(std::memory_order_relaxed) | ((i & 63) ? ((1ull << (i & 63)) - 1) : 0);
+        if (word != ~0ull) return std::min<uint64_t>((w << 6) + (unsigned)__builtin_ctzll(~word), N);
+        i = (w + 1) << 6;
+    }
+    return N;
+}
+
+// First busy granule in [start, start+n), or start+n if the run is free (read-only probe).
+uint64_t first_busy(std::atomic<uint64_t> *bm, uint64_t start, uint64_t n) {
+    uint64_t i = start, end = start + n;
+    while (i < end) {
+        uint64_t w = i >> 6;
+        unsigned lo = (unsigned)(i & 63);
+        unsigned hi = (unsigned)std::min<uint64_t>(64, lo + (end - i));
+        uint64_t busy = bm[w].load(std::memory_order_relaxed) & bits(lo, hi);
+        if (busy) return (w << 6) + (unsigned)__builtin_ctzll(busy);
+        i += hi - lo;
+    }
+    return end;
+}
+
+// Find and claim a free run of n granules in [lo, hi).  Returns its start or UINT64_MAX.
+uint64_t find_run(std::atomic<uint64_t> *bm, uint64_t lo, uint64_t hi, uint64_t n) {
+    uint64_t i = lo;
+    while (i + n <= hi) {
+        i = next_free(bm, i, hi);
+        if (i + n > hi) break;
+        uint64_t b = first_busy(bm, i, n);
+        if (b < i + n) {
+            i = b + 1;
+            continue;
+        }
+        uint64_t conflict = 0;
+        if (bitmap_claim(bm, i, n, &conflict)) return i;
+        i = conflict + 1;
+    }
+    return UINT64_MAX;
+}
+} // namespace
 
 uint64_t default_granule(uint64_t pool_bytes, Tier tier) {
     uint64_t g = tier == TIER_GPU ? (64ull << 10) : (4ull << 10);
@@ -140,8 +176,12 @@ size_t table_segment_bytes(uint64_t gpu_pool_bytes, uint64_t host_pool_bytes, ui
     if (!gg) gg = default_granule(gpu_pool_bytes, TIER_GPU);
     if (!hg) hg = default_granule(host_pool_bytes, TIER_HOST);
     size_t n_gpu = gpu_pool_bytes / gg, n_host = host_pool_bytes / hg;
-    return round_up(sizeof(TableHeader), 4096) + round_up(n_gpu * sizeof(Region), 4096) +
-           round_up(n_host * sizeof(Region), 4096);
+    size_t total = round_up(sizeof(TableHeader), 4096);
+    for (size_t n : {n_gpu, n_host}) {
+        total += round_up(n * sizeof(Region), 4096);
+        total += round_up((n + 63) / 64 * 8, 4096);
+    }
+    return total;
 }
 
 void table_format(void *base, size_t seg_bytes, int rank, int n_ranks, int daemon_pid,
@@ -170,6 +210,14 @@ void table_format(void *base, size_t seg_bytes, int rank, int n_ranks, int daemo
         p.tier = t;
         p.regions_offset = off;
         off += round_up((size_t)p.n_granules * sizeof(Region), 4096);
+        p.bitmap_offset = off;
+        p.bitmap_words = (p.n_granules + 63) / 64;
+        off += round_up((size_t)p.bitmap_words * 8, 4096);
+        // granules past the end of the pool are permanently taken
+        if (p.n_granules & 63) {
+            auto *bm = table_bitmap(h, t);
+            bm[p.bitmap_words - 1].store(~((1ull << (p.n_granules & 63)) - 1), std::memory_order_relaxed);
+        }
     }
     OCM_BUG(off > seg_bytes);
 }
@@ -180,8 +228,10 @@ bool table_validate(const TableHeader *h, size_t mapped) {
     if (h->segment_bytes > mapped) return false;
     for (int t = 0; t < TIER_COUNT; ++t) {
         const PoolDesc &p = h->pool[t];
-        if (p.n_granules && (p.regions_offset + (uint64_t)p.n_granules * sizeof(Region) > mapped)) return false;
-        if (p.n_granules && (p.granule & (p.granule - 1))) return false;
+        if (!p.n_granules) continue;
+        if (p.regions_offset + (uint64_t)p.n_granules * sizeof(Region) > mapped) return false;
+        if (p.bitmap_offset + (uint64_t)p.bitmap_words * 8 > mapped) return false;
+        if (p.granule & (p.granule - 1)) return false;
     }
     return true;
 }
@@ -192,39 +242,21 @@ int pool_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int rank, Bloc
     PoolDesc &p = h->pool[tier];
     if (p.n_granules == 0) return OCM_ENOMEM;
     if (bytes == 0) bytes = 1;
-    uint64_t need = (bytes + p.granule - 1) / p.granule;
-    int cls = class_of(need);
-    if (cls < 0 || class_granules(cls) > p.n_granules) return OCM_ENOMEM;
-    Region *regs = table_regions(h, tier);
+    const uint64_t n = (bytes + p.granule - 1) / p.granule;
+    if (n > p.n_granules) return OCM_ENOMEM;
+    std::atomic<uint64_t> *bm = table_bitmap(h, tier);
+    const uint64_t N = p.n_granules;
+    uint64_t hint = p.hint.load(std::memory_order_relaxed);
+    if (hint >= N) hint = 0;
+    uint64_t start = find_run(bm, hint, N, n);
+    if (start == UINT64_MAX && hint) start = find_run(bm, 0, std::min<uint64_t>(N, hint + n), n);
+    if (start == UINT64_MAX) return OCM_ENOMEM;
+    p.hint.store(start + n >= N ? 0 : start + n, std::memory_order_relaxed);
 
-    uint32_t idx_p1 = stack_pop(p.class_head[cls], regs);
-    int got_cls = cls;
-    if (!idx_p1) {
-        // carve a fresh block from the frontier
-        uint32_t g = class_granules(cls);
-        uint64_t f = p.frontier.load(std::memory_order_relaxed);
-        for (;;) {
-            if (f + g > p.n_granules) break;
-            if (p.frontier.compare_exchange_weak(f, f + g, std::memory_order_acq_rel)) {
-                idx_p1 = (uint32_t)f + 1;
-                regs[f].cls_plus1 = (uint32_t)cls + 1;
-                break;
-            }
-        }
-        if (!idx_p1) {
-            // frontier exhausted: the tail may still fit an exact (unrounded) block
-            f = p.frontier.load(std::memory_order_relaxed);
-            // otherwise reuse a larger free block whole (no splitting)
-            for (int c = cls + 1; c < kNumClasses && class_granules(c) <= p.n_granules; ++c) {
-                idx_p1 = stack_pop(p.class_head[c], regs);
-                if (idx_p1) { got_cls = c; break; }
-            }
-        }
-    }
-    if (!idx_p1) return OCM_ENOMEM;
-    uint32_t idx = idx_p1 - 1;
-    Region &r = regs[idx];
-    uint64_t block_bytes = (uint64_t)class_granules(got_cls) * p.granule;
+    Region *regs = table_regions(h, tier);
+    Region &r = regs[start];
+    const uint64_t block_bytes = n * p.granule;
+    r.n_granules = (uint32_t)n;
     r.owner_pid = pid;
     r.owner_rank = rank;
     r.bytes = bytes;
@@ -236,9 +268,9 @@ int pool_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int rank, Bloc
     p.used_bytes.fetch_add(block_bytes, std::memory_order_relaxed);
     p.live.fetch_add(1, std::memory_order_relaxed);
     p.total_allocs.fetch_add(1, std::memory_order_relaxed);
-    out->region = idx;
+    out->region = (uint32_t)start;
     out->generation = r.generation;
-    out->offset = (uint64_t)idx * p.granule;
+    out->offset = start * p.granule;
     out->block_bytes = block_bytes;
     out->id = r.id;
     return OCM_OK;
@@ -250,13 +282,13 @@ int pool_free(TableHeader *h, int tier, uint32_t region, uint64_t id) {
     if (region >= p.n_granules) return OCM_EINVAL;
     Region *regs = table_regions(h, tier);
     Region &r = regs[region];
-    if (r.cls_plus1 == 0) return OCM_ESTALE;
     if (r.state.load(std::memory_order_acquire) != REGION_LIVE || r.id != id) return OCM_ESTALE;
-    bool scrub = h->scrub_enabled.load(std::memory_order_relaxed) != 0;
+    const bool scrub = h->scrub_enabled.load(std::memory_order_relaxed) != 0;
+    const uint32_t n = r.n_granules;
     uint32_t expect = REGION_LIVE;
     if (!r.state.compare_exchange_strong(expect, scrub ? REGION_DIRTY : REGION_FREE, std::memory_order_acq_rel))
         return OCM_ESTALE; // lost a race with another free / the reclaimer
-    uint64_t block_bytes = (uint64_t)class_granules((int)r.cls_plus1 - 1) * p.granule;
+    const uint64_t block_bytes = (uint64_t)n * p.granule;
     p.used_bytes.fetch_sub(block_bytes, std::memory_order_relaxed);
     p.live.fetch_sub(1, std::memory_order_relaxed);
     p.total_frees.fetch_add(1, std::memory_order_relaxed);
@@ -264,7 +296,7 @@ int pool_free(TableHeader *h, int tier, uint32_t region, uint64_t id) {
         p.dirty_bytes.fetch_add(block_bytes, std::memory_order_relaxed);
         stack_push(p.dirty_head, regs, region);
     } else {
-        stack_push(p.class_head[r.cls_plus1 - 1], regs, region);
+        bitmap_clear(table_bitmap(h, tier), region, n);
     }
     return OCM_OK;
 }
@@ -283,8 +315,7 @@ size_t pool_take_dirty(TableHeader *h, int tier, std::vector<DirtyBlock> *out) {
         Region &r = regs[ip1 - 1];
         uint32_t nxt = r.next.load(std::memory_order_relaxed);
         r.state.store(REGION_SCRUBBING, std::memory_order_relaxed);
-        uint64_t bb = (uint64_t)class_granules((int)r.cls_plus1 - 1) * p.granule;
-        out->push_back({ip1 - 1, (uint64_t)(ip1 - 1) * p.granule, bb});
+        out->push_back({ip1 - 1, (uint64_t)(ip1 - 1) * p.granule, (uint64_t)r.n_granules * p.granule});
         ++n;
         ip1 = nxt;
     }
@@ -293,55 +324,77 @@ size_t pool_take_dirty(TableHeader *h, int tier, std::vector<DirtyBlock> *out) {
 
 void pool_release_scrubbed(TableHeader *h, int tier, uint32_t region) {
     PoolDesc &p = h->pool[tier];
-    Region *regs = table_regions(h, tier);
-    Region &r = regs[region];
-    uint64_t bb = (uint64_t)class_granules((int)r.cls_plus1 - 1) * p.granule;
-    p.dirty_bytes.fetch_sub(bb, std::memory_order_relaxed);
+    Region &r = table_regions(h, tier)[region];
+    const uint32_t n = r.n_granules;
+    p.dirty_bytes.fetch_sub((uint64_t)n * p.granule, std::memory_order_relaxed);
     r.state.store(REGION_FREE, std::memory_order_release);
-    stack_push(p.class_head[r.cls_plus1 - 1], regs, region);
+    bitmap_clear(table_bitmap(h, tier), region, n);
+}
+
+uint64_t pool_scrub_host_inline(TableHeader *h, void *host_pool_base) {
+    if (!host_pool_base) return 0;
+    std::vector<DirtyBlock> blocks;
+    if (!pool_take_dirty(h, TIER_HOST, &blocks)) return 0;
+    Region *regs = table_regions(h, TIER_HOST);
+    uint64_t total = 0;
+    for (auto &b : blocks) {
+        // only the part the owner could touch needs clearing
+        uint64_t n = std::min<uint64_t>(b.bytes, (regs[b.region].bytes + 4095) & ~4095ull);
+        memset(static_cast<char *>(host_pool_base) + b.offset, 0, n);
+        total += b.bytes;
+        pool_release_scrubbed(h, TIER_HOST, b.region);
+    }
+    return total;
+}
+
+// Visit the start granule of every block whose bits are set.  Blocks are found by
+// walking the bitmap: a set bit whose Region is not FREE starts a block.
+template <typename F> static void for_each_block(TableHeader *h, int tier, F &&fn) {
+    PoolDesc &p = h->pool[tier];
+    std::atomic<uint64_t> *bm = table_bitmap(h, tier);
+    Region *regs = table_regions(h, tier);
+    const uint64_t N = p.n_granules;
+    for (uint64_t w = 0; w < p.bitmap_words; ++w) {
+        uint64_t word = bm[w].load(std::memory_order_acquire);
+        while (word) {
+            unsigned b = (unsigned)__builtin_ctzll(word);
+            word &= word - 1;
+            uint64_t i = (w << 6) + b;
+            if (i >= N) break;
+            Region &r = regs[i];
+            if (r.state.load(std::memory_order_acquire) != REGION_FREE) fn((uint32_t)i, r);
+        }
+    }
 }
 
 size_t pool_reclaim(TableHeader *h, int tier, bool (*pred)(int, int, void *), void *ctx, uint64_t *bytes_out,
                     std::vector<BlockRef> *reclaimed) {
     PoolDesc &p = h->pool[tier];
     if (!p.n_granules) return 0;
-    Region *regs = table_regions(h, tier);
-    uint64_t frontier = p.frontier.load(std::memory_order_acquire);
     size_t n = 0;
-    for (uint64_t i = 0; i < frontier;) {
-        Region &r = regs[i];
-        if (r.cls_plus1 == 0) break; // carve in progress; next sweep sees it
-        uint32_t g = class_granules((int)r.cls_plus1 - 1);
-        if (r.state.load(std::memory_order_acquire) == REGION_LIVE && pred(r.owner_pid, r.owner_rank, ctx)) {
-            uint64_t id = r.id;
-            if (pool_free(h, tier, (uint32_t)i, id) == OCM_OK) {
-                ++n;
-                if (bytes_out) *bytes_out += (uint64_t)g * p.granule;
-                if (reclaimed) {
-                    BlockRef b;
-                    b.region = (uint32_t)i; b.id = id; b.offset = i * p.granule;
-                    b.block_bytes = (uint64_t)g * p.granule; b.generation = r.generation;
-                    reclaimed->push_back(b);
-                }
-            }
+    for_each_block(h, tier, [&](uint32_t i, Region &r) {
+        if (r.state.load(std::memory_order_acquire) != REGION_LIVE || !pred(r.owner_pid, r.owner_rank, ctx)) return;
+        const uint64_t id = r.id;
+        const uint32_t g = r.n_granules;
+        if (pool_free(h, tier, i, id) != OCM_OK) return;
+        ++n;
+        if (bytes_out) *bytes_out += (uint64_t)g * p.granule;
+        if (reclaimed) {
+            BlockRef b;
+            b.region = i; b.id = id; b.offset = (uint64_t)i * p.granule;
+            b.block_bytes = (uint64_t)g * p.granule; b.generation = r.generation;
+            reclaimed->push_back(b);
         }
-        i += g;
-    }
+    });
     return n;
 }
 
 size_t pool_count_live(TableHeader *h, int tier) {
-    PoolDesc &p = h->pool[tier];
-    if (!p.n_granules) return 0;
-    Region *regs = table_regions(h, tier);
-    uint64_t frontier = p.frontier.load(std::memory_order_acquire);
+    if (!h->pool[tier].n_granules) return 0;
     size_t n = 0;
-    for (uint64_t i = 0; i < frontier;) {
-        Region &r = regs[i];
-        if (r.cls_plus1 == 0) break;
+    for_each_block(h, tier, [&](uint32_t, Region &r) {
         if (r.state.load(std::memory_order_acquire) == REGION_LIVE) ++n;
-        i += class_granules((int)r.cls_plus1 - 1);
-    }
+    });
     return n;
 }
 

@@ -13,12 +13,15 @@
 // rank-0 bookkeeping in a mutex-protected list it never prunes,
 // src/alloc.c:133-137, src/mem.c:220-229).
 //
-// Allocator: size-class blocks (8 linear classes, then 4 per doubling) carved
-// from a bump frontier; freed blocks go to a per-class Treiber stack (ABA tag
-// in the upper half of the head word).  Freed blocks first pass through a
-// "dirty" stack so that the owner daemon can zero them (the reference
-// zero-fills remote buffers at allocation, src/alloc.c:171,
-// src/extoll_client.c:46 - here the cost is paid off the allocation path).
+// Allocator: one bit per granule in a shared bitmap.  A block is a run of
+// granules claimed word by word with compare-and-swap (rolled back if a later
+// word is contended); releasing clears the bits, so free space coalesces by
+// construction and a pool never fragments into unusable size classes.  Freed
+// blocks first pass through a "dirty" Treiber stack (ABA tag in the upper half
+// of the head word) so that the owner daemon can zero them before their bits
+// are cleared (the reference zero-fills remote buffers at allocation,
+// src/alloc.c:171, src/extoll_client.c:46 - here the cost is paid off the
+// allocation path).
 #pragma once
 #include "msg.hpp"
 #include <atomic>
@@ -31,15 +34,14 @@ namespace ocm {
 
 constexpr uint64_t kTableMagic   = 0x4F434D5441424C45ull; // "OCMTABLE"
 constexpr uint32_t kTableVersion = 3;
-constexpr int      kNumClasses   = 128;
 constexpr uint32_t kMaxGranules  = 1u << 18;
 
 enum RegionState : uint32_t { REGION_FREE = 0, REGION_LIVE = 1, REGION_DIRTY = 2, REGION_SCRUBBING = 3 };
 
 struct alignas(64) Region {
     std::atomic<uint32_t> state;
-    uint32_t              cls_plus1;   // size class + 1 of the block starting here; 0 = never carved
-    std::atomic<uint32_t> next;        // stack link: granule index + 1, 0 = end
+    uint32_t              n_granules;  // length of the block starting here (valid while not FREE)
+    std::atomic<uint32_t> next;        // dirty-stack link: granule index + 1, 0 = end
     uint32_t              generation;
     int32_t               owner_pid;
     int32_t               owner_rank;
@@ -57,14 +59,16 @@ struct PoolDesc {
     uint32_t n_granules;
     uint32_t tier;
     uint64_t regions_offset;   // from segment start
-    std::atomic<uint64_t> frontier;      // granules handed out by the bump allocator
+    uint64_t bitmap_offset;    // from segment start; one bit per granule, 1 = taken
+    uint32_t bitmap_words;
+    uint32_t pad;
+    std::atomic<uint64_t> hint;          // granule where the next search starts (first fit, rotating)
     std::atomic<uint64_t> used_bytes;    // sum of live block bytes
     std::atomic<uint64_t> live;
     std::atomic<uint64_t> total_allocs;
     std::atomic<uint64_t> total_frees;
     std::atomic<uint64_t> dirty_head;    // {tag:32, idx+1:32}
     std::atomic<uint64_t> dirty_bytes;
-    std::atomic<uint64_t> class_head[kNumClasses];
 };
 
 enum GpuShareMode : uint32_t { GPU_SHARE_NONE = 0, GPU_SHARE_VMM_FD = 1, GPU_SHARE_CUDA_IPC = 2 };
@@ -113,10 +117,10 @@ struct ClusterTable {
     NodeSlot node[kMaxRanks];
 };
 
-// ---- size classes ------------------------------------------------------
-uint32_t class_granules(int cls);           // block size of a class, in granules
-int      class_of(uint64_t granules);       // smallest class that fits; -1 if none
 uint64_t default_granule(uint64_t pool_bytes, Tier tier);
+inline std::atomic<uint64_t> *table_bitmap(TableHeader *h, int tier) {
+    return reinterpret_cast<std::atomic<uint64_t> *>(reinterpret_cast<char *>(h) + h->pool[tier].bitmap_offset);
+}
 
 // ---- segment lifecycle (POSIX shm) ---------------------------------------
 struct ShmMapping {
@@ -160,8 +164,15 @@ int pool_free(TableHeader *h, int tier, uint32_t region, uint64_t id);
 struct DirtyBlock { uint32_t region; uint64_t offset; uint64_t bytes; };
 // Detach the whole dirty stack (blocks become SCRUBBING).
 size_t pool_take_dirty(TableHeader *h, int tier, std::vector<DirtyBlock> *out);
-// Return a scrubbed block to its class stack.
+// Return a scrubbed block to the pool (clears its bits).
 void pool_release_scrubbed(TableHeader *h, int tier, uint32_t region);
+// Any process that maps the pinned-host pool may help the owner: detach the dirty
+// host blocks, zero them and release them.  Returns bytes scrubbed.
+uint64_t pool_scrub_host_inline(TableHeader *h, void *host_pool_base);
+// True while released blocks are still waiting to be zeroed in this tier.
+inline bool pool_has_dirty(const TableHeader *h, int tier) {
+    return h->pool[tier].dirty_bytes.load(std::memory_order_acquire) != 0;
+}
 // Walk carved blocks; for LIVE blocks call pred(owner_pid, owner_rank) and free
 // those for which it returns true.  Returns blocks reclaimed; adds their bytes
 // to *bytes_out.

@@ -637,6 +637,12 @@ int Daemon::do_alloc_local(Message &m) {
     if (a.tier >= TIER_COUNT) return OCM_EINVAL;
     BlockRef b;
     int err = pool_alloc(tbl_, (int)a.tier, a.bytes, m.pid, m.rank, &b);
+    // blocks waiting to be zeroed still hold their space: give the scrubber a bounded moment
+    for (uint64_t t0 = now_ns(); err == OCM_ENOMEM && pool_has_dirty(tbl_, (int)a.tier) && now_ns() - t0 < 50000000ull;) {
+        if (a.tier == TIER_HOST) pool_scrub_host_inline(tbl_, host_map_.base);
+        else usleep(100);
+        err = pool_alloc(tbl_, (int)a.tier, a.bytes, m.pid, m.rank, &b);
+    }
     if (err) return err;
     a.rem_alloc_id = b.id;
     a.offset = b.offset;

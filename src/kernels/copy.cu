@@ -41,23 +41,6 @@ struct CopyArgs {
     unsigned      *ticket;
 };
 
-// Elect the last CTA and publish completion.  Called by one thread per CTA
-// after a CTA-wide barrier that follows the CTA's last store.
-__device__ __forceinline__ void finish_and_signal(uint64_t *signal, unsigned *ticket) {
-    __threadfence_system();
-    bool last = true;
-    if (gridDim.x > 1) {
-        if (ticket == nullptr) return; // nobody to notify
-        unsigned t = atomicAdd(ticket, 1u);
-        last = (t == gridDim.x - 1);
-        if (last) atomicExch(ticket, 0u); // ready for the next launch
-    }
-    if (last && signal) {
-        __threadfence_system();
-        red_release_sys_add(signal, 1ull);
-    }
-}
-
 __global__ void __launch_bounds__(kMaxAgents * 32, 1) ocm_copy_bulk_kernel(CopyArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full[kMaxAgents][kMaxStages];

@@ -56,6 +56,9 @@ struct StridedDesc {
 };
 cudaError_t launch_strided(const StridedDesc &d, uint64_t *signal, unsigned *ticket, cudaStream_t stream,
                            unsigned long long *launches = nullptr);
+#ifdef __CUDACC__
+__host__ __device__
+#endif
 inline size_t dtype_size(int dt) { return dt == DT_F32 ? 4 : dt == DT_BF16 ? 2 : 1; }
 
 // ---- K6: replicated put ---------------------------------------------------------
@@ -76,6 +79,12 @@ struct GupsTable {
 };
 cudaError_t launch_gups(const GupsTable &t, uint64_t n_updates, uint64_t seed, cudaStream_t stream);
 cudaError_t launch_gups_init(const GupsTable &t, int my_rank, cudaStream_t stream);
+
+// ---- K8: radix sort of u64 keys -------------------------------------------------------
+// scratch holds the per-CTA digit histograms and their scanned offsets.
+size_t sort_scratch_bytes(uint64_t n, int *ctas_out = nullptr);
+cudaError_t launch_sort_u64(uint64_t *keys, uint64_t *tmp, uint64_t n, void *scratch, size_t scratch_bytes,
+                            cudaStream_t stream, unsigned long long *launches = nullptr);
 
 int num_sms(int device = -1);
 

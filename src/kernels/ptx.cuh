@@ -148,4 +148,21 @@ __device__ __forceinline__ void mbar_arrive_remote(uint64_t *bar, uint32_t cta) 
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
 }
 
+// Elect the last CTA and publish completion.  Called by one thread per CTA
+// after a CTA-wide barrier that follows the CTA's last store.
+__device__ __forceinline__ void finish_and_signal(uint64_t *signal, unsigned *ticket) {
+    __threadfence_system();
+    bool last = true;
+    if (gridDim.x > 1) {
+        if (ticket == nullptr) return; // nobody to notify
+        unsigned t = atomicAdd(ticket, 1u);
+        last = (t == gridDim.x - 1);
+        if (last) atomicExch(ticket, 0u); // ready for the next launch
+    }
+    if (last && signal) {
+        __threadfence_system();
+        red_release_sys_add(signal, 1ull);
+    }
+}
+
 } // namespace ocmk

@@ -89,6 +89,12 @@ int daemon_call(Message &m, int timeout_ms) {
         if (r == 0) {
             // detect a dead daemon instead of waiting out the timeout
             if (c.daemon_pid > 0 && kill(c.daemon_pid, 0) != 0 && errno == ESRCH) return OCM_ENODAEMON;
+            // a killed-but-unreaped daemon still has a pid: its heartbeat (20 ms period) tells the truth
+            const TableHeader *hb = c.view[c.rank].hdr;
+            if (hb) {
+                uint64_t beat = hb->heartbeat_ns.load(std::memory_order_relaxed);
+                if (beat && mono_ns() > beat + 1500000000ull) return OCM_ENODAEMON;
+            }
             continue;
         }
         if (!rep.valid() || rep.seq != m.seq || rep.type != want_type) {
@@ -217,14 +223,21 @@ static int alloc_side(uint32_t type, uint64_t bytes, int policy, int explicit_ra
         req.type = type;
         req.policy = (uint32_t)policy;
         req.flags = flags;
-        int err = governor_place(c.cluster, req, &a);
-        if (err) return err;
-        RankView *v = get_view(a.remote_rank, a.tier == TIER_GPU);
         BlockRef b;
-        err = v ? pool_alloc(v->hdr, (int)a.tier, bytes, (int)getpid(), c.rank, &b) : OCM_ENODAEMON;
-        if (err) {
+        const uint64_t t_start = mono_ns();
+        for (;;) {
+            int err = governor_place(c.cluster, req, &a);
+            if (err) return err;
+            RankView *v = get_view(a.remote_rank, a.tier == TIER_GPU);
+            err = v ? pool_alloc(v->hdr, (int)a.tier, bytes, (int)getpid(), c.rank, &b) : OCM_ENODAEMON;
+            if (!err) break;
             governor_release(c.cluster, a.remote_rank, (int)a.tier, bytes);
-            return err;
+            // Released blocks are unavailable until zeroed.  Back-pressure instead of failing while the
+            // owner's scrubber catches up; for the pinned-host tier lend it a hand.
+            if (err != OCM_ENOMEM || !v || !pool_has_dirty(v->hdr, (int)a.tier)) return err;
+            if (mono_ns() - t_start > 2000000000ull) return err;
+            if (a.tier == TIER_HOST && v->host_map.base) pool_scrub_host_inline(v->hdr, v->host_map.base);
+            else usleep(50);
         }
         a.rem_alloc_id = b.id; a.offset = b.offset; a.block_bytes = b.block_bytes;
         a.region = b.region; a.generation = b.generation;

@@ -139,7 +139,8 @@ static int do_copy(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p,
     } else if (dfar && !sfar) {
         // local -> pair: hop 1 into the window, hop 2 window -> far side
         if (!dst->local.valid()) {
-            err = side_copy(*dfar, p->dest_offset_2, nullptr, 0, src->local, p->src_offset, n, dfar->rec, stream, used);
+            // window-less pair: a single hop, src_offset/dest_offset index source/destination
+            err = side_copy(*dfar, p->dest_offset, nullptr, 0, src->local, p->src_offset, n, dfar->rec, stream, used);
         } else if (p->src_offset_2 == p->dest_offset) {
             err = side_copy(*dfar, p->dest_offset_2, &dst->local, p->dest_offset, src->local, p->src_offset, n,
                             dfar->rec, stream, used);
@@ -151,7 +152,7 @@ static int do_copy(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p,
     } else if (!dfar && sfar) {
         // pair -> local: hop 1 far side -> window, hop 2 window -> destination
         if (!src->local.valid()) {
-            err = side_copy(dst->local, p->dest_offset_2, nullptr, 0, *sfar, p->dest_offset, n, dst->local.rec, stream, used);
+            err = side_copy(dst->local, p->dest_offset, nullptr, 0, *sfar, p->src_offset, n, dst->local.rec, stream, used);
         } else if (p->src_offset_2 == p->src_offset) {
             err = side_copy(dst->local, p->dest_offset_2, &src->local, p->src_offset, *sfar, p->dest_offset, n,
                             dst->local.rec, stream, used);

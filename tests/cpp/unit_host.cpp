@@ -139,22 +139,11 @@ static TableHeader *fresh_table(std::vector<char> &buf, uint64_t gpu, uint64_t h
 }
 
 static void t_tables() {
-    // size classes: monotone, waste bounded by 25 %
-    uint32_t prev = 0;
-    for (int c = 0; c < kNumClasses && class_granules(c) != 0xFFFFFFFFu; ++c) {
-        CHECK(class_granules(c) > prev);
-        prev = class_granules(c);
-    }
-    for (uint64_t g : {1ull, 2ull, 7ull, 9ull, 17ull, 100ull, 1000ull, 65537ull, 1000000ull}) {
-        int c = class_of(g);
-        CHECK(c >= 0 && class_granules(c) >= g);
-        CHECK((double)class_granules(c) <= 1.25 * (double)g + 1.0);
-        CHECK(c == 0 || class_granules(c - 1) < g);
-    }
     std::vector<char> buf;
     TableHeader *h = fresh_table(buf, 64ull << 20, 1ull << 20); // 1024 GPU granules of 64 KiB, 256 host granules
     CHECK(h->pool[TIER_GPU].granule == 65536 && h->pool[TIER_GPU].n_granules == 1024);
     CHECK(h->pool[TIER_HOST].granule == 4096 && h->pool[TIER_HOST].n_granules == 256);
+    CHECK(default_granule(160ull << 30, TIER_GPU) == (1ull << 20)); // 160 GiB pool -> <= 2^18 granules
     BlockRef a, b, c;
     CHECK(pool_alloc(h, TIER_GPU, 100, 11, 0, &a) == OCM_OK && a.offset == 0 && a.block_bytes == 65536);
     CHECK(pool_alloc(h, TIER_GPU, 65537, 11, 0, &b) == OCM_OK && b.offset == 65536 && b.block_bytes == 131072);
@@ -172,30 +161,31 @@ static void t_tables() {
     CHECK(pool_take_dirty(h, TIER_GPU, &dirty) == 1 && dirty[0].region == a.region && dirty[0].bytes == 65536);
     CHECK(regs[a.region].state.load() == REGION_SCRUBBING);
     pool_release_scrubbed(h, TIER_GPU, a.region);
-    BlockRef d;
-    CHECK(pool_alloc(h, TIER_GPU, 4096, 13, 0, &d) == OCM_OK && d.offset == a.offset && d.generation == a.generation + 1);
-    // exhaustion and capacity accounting
-    BlockRef big;
-    CHECK(pool_alloc(h, TIER_GPU, 128ull << 20, 1, 0, &big) == OCM_ENOMEM);
+    CHECK(regs[a.region].state.load() == REGION_FREE);
+    // exhaustion: the rest of the pool in one-granule blocks, then the hole left by `a` is found too
+    CHECK(pool_alloc(h, TIER_GPU, 128ull << 20, 1, 0, &c) == OCM_ENOMEM);
     std::vector<BlockRef> many;
     for (;;) {
         BlockRef x;
         if (pool_alloc(h, TIER_GPU, 65536, 14, 0, &x) != OCM_OK) break;
         many.push_back(x);
     }
-    CHECK(many.size() == 1024 - 4);
-    CHECK(pool_count_live(h, TIER_GPU) == many.size() + 3);
-    // without scrubbing blocks are reusable at once; a bigger free block serves a smaller request
+    CHECK(many.size() == 1024 - 3);
+    CHECK(regs[a.region].generation == a.generation + 1); // first-fit wrapped around into the scrubbed hole
+    CHECK(pool_count_live(h, TIER_GPU) == many.size() + 2);
+    CHECK(h->pool[TIER_GPU].used_bytes.load() == h->pool[TIER_GPU].bytes);
+    // coalescing: free everything owned by pid 14, then one block spanning all of it fits
     h->scrub_enabled.store(0);
-    CHECK(pool_free(h, TIER_GPU, b.region, b.id) == OCM_OK);
-    BlockRef e;
-    CHECK(pool_alloc(h, TIER_GPU, 10, 15, 0, &e) == OCM_OK && e.offset == b.offset && e.block_bytes == 131072);
-    // reclaim by owner
     uint64_t bytes = 0;
     auto pred = [](int pid, int, void *) { return pid == 14; };
     CHECK(pool_reclaim(h, TIER_GPU, pred, nullptr, &bytes) == many.size());
     CHECK(bytes == many.size() * 65536ull);
-    CHECK(pool_count_live(h, TIER_GPU) == 3);
+    CHECK(pool_count_live(h, TIER_GPU) == 2);
+    BlockRef big;
+    CHECK(pool_alloc(h, TIER_GPU, (1024 - 4) * 65536ull, 15, 0, &big) == OCM_OK && big.offset == 4 * 65536ull);
+    CHECK(pool_alloc(h, TIER_GPU, 2 * 65536, 15, 0, &c) == OCM_ENOMEM);   // only the single-granule hole is left
+    CHECK(pool_alloc(h, TIER_GPU, 65536, 15, 0, &c) == OCM_OK && c.offset == 0);
+    CHECK(pool_free(h, TIER_GPU, big.region, big.id) == OCM_OK);
     // host tier independent
     BlockRef hb;
     CHECK(pool_alloc(h, TIER_HOST, 5000, 1, 0, &hb) == OCM_OK && hb.block_bytes == 8192);

@@ -1,0 +1,243 @@
+"""Daemon + libocm integration on CPU: several ranks on one host, full protocol, no GPU.
+
+Models the reference's end-to-end program (reference test/ocm_test.c) and adds what it never tested
+(SURVEY section 4): data verification, both allocation paths, placement, accounting, double free,
+app-death reclamation, daemon-death detection, concurrent clients.
+"""
+import json
+import os
+import signal
+import subprocess
+import sys
+import time
+
+import pytest
+
+import oncilla_b200 as ocm
+from conftest import BIN, REPO, run_app, run_py
+
+
+def _ok(r):
+    assert r.returncode == 0, f"rc={r.returncode}\n{r.stdout}\n{r.stderr}"
+    return r.stdout
+
+
+@pytest.mark.parametrize("path", ["fast", "daemon"])
+@pytest.mark.parametrize("test,args", [(1, ["1", "2", "1"]), (1, ["1", "2", "3"]), (1, ["1", "2", "8"]),
+                                       (2, ["1", "1", "3"]), (3, ["1", "1", "1"]), (4, ["0.25", "0.25", "3", "2"])])
+def test_ocm_test_program(cluster2, path, test, args):
+    out = _ok(run_app(cluster2, 1, [BIN / "ocm_test", test, *args], env_extra={"OCM_ALLOC_PATH": path}))
+    assert "pass: OCM test completed successfully" in out
+    assert "FAIL" not in out
+
+
+API_SNIPPET = r"""
+import json, torch, ctypes
+import oncilla_b200 as ocm
+ocm.init()
+res = {"rank": ocm.rank(), "n": ocm.num_ranks(), "dev": ocm.device()}
+# local host
+h = ocm.alloc(ocm.OCM_LOCAL_HOST, 1 << 20)
+res["host_kind"] = h.kind; res["host_remote"] = h.is_remote; res["host_rsz"] = h.remote_bytes
+t = h.local_tensor()
+res["host_zero"] = int(t.sum())
+t[:] = torch.arange(1 << 20, dtype=torch.int64).to(torch.uint8)
+# remote pair, legacy name -> pinned host on the neighbour
+r = ocm.alloc(ocm.OCM_REMOTE_RDMA, 1 << 20, 2 << 20)
+res["pair_kind"] = r.kind; res["pair_remote"] = r.is_remote; res["pair_rank"] = r.remote_rank
+res["pair_rsz"] = r.remote_bytes; res["far_zero"] = int(r.remote_tensor().sum())
+ocm.copy(r, h, 1 << 20)                       # host -> window + far side
+res["sig"] = r.signal()
+res["far_eq"] = bool(torch.equal(r.remote_tensor()[: 1 << 20], t))
+res["win_eq"] = bool(torch.equal(r.local_tensor(), t))
+# one-sided at offsets: window[4096:8192] -> far[1 MiB + 100 : ...]
+r.put(4096, src_offset=4096, dest_offset=(1 << 20) + 100)
+res["off_eq"] = bool(torch.equal(r.remote_tensor()[(1 << 20) + 100:(1 << 20) + 100 + 4096], t[4096:8192]))
+res["sig2"] = r.signal()
+# read back through a second host allocation (op_flag=0 flips the direction)
+h2 = ocm.alloc(ocm.OCM_LOCAL_HOST, 1 << 20)
+ocm.copy(r, h2, 1 << 20, op_flag=0)
+res["read_eq"] = bool(torch.equal(h2.local_tensor(), t))
+# two-hop with distinct offsets: host[0:1024] -> window[2048:3072]; window[512:1536] -> far[0:1024]
+before = r.local_tensor()[512:1536].clone()
+ocm.copy(r, h, 1024, src_offset=0, dest_offset=2048, src_offset_2=512, dest_offset_2=0)
+res["hop1"] = bool(torch.equal(r.local_tensor()[2048:3072], t[:1024]))
+res["hop2"] = bool(torch.equal(r.remote_tensor()[:1024], before))
+# pair -> pair third-party copy
+r2 = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 1 << 20, policy=ocm.POLICY_SELF)
+res["self_rank"] = r2.remote_rank
+ocm.copy(r2, r, 1 << 20)
+res["p2p_eq"] = bool(torch.equal(r2.remote_tensor(), r.remote_tensor()[: 1 << 20]))
+# errors
+try:
+    r.put(10, dest_offset=(2 << 20))
+    res["range_err"] = False
+except ocm.OcmError as e:
+    res["range_err"] = e.err == 5
+st = ocm.stats()
+res["live"] = st["allocs_live"]; res["fast"] = st["fast_path_allocs"]; res["slow"] = st["slow_path_allocs"]
+rs = ocm.stats(rank=r.remote_rank)
+res["remote_pool_used"] = rs["pool_host_used"]
+for a in (h, h2, r, r2): a.free()
+try:
+    h.free(); res["double_free_noop"] = True
+except Exception:
+    res["double_free_noop"] = False
+res["live_end"] = ocm.stats()["allocs_live"]
+ocm.tini()
+print("RESULT " + json.dumps(res))
+"""
+
+
+@pytest.mark.parametrize("path", ["fast", "daemon"])
+def test_python_api_host_kinds(cluster2, path):
+    out = _ok(run_py(cluster2, 0, API_SNIPPET, env_extra={"OCM_ALLOC_PATH": path}))
+    res = json.loads(out.split("RESULT ", 1)[1])
+    assert res["rank"] == 0 and res["n"] == 2 and res["dev"] == -1
+    assert res["host_kind"] == ocm.OCM_LOCAL_HOST and not res["host_remote"] and res["host_rsz"] == -1
+    assert res["host_zero"] == 0 and res["far_zero"] == 0            # zero-filled like the reference's calloc
+    assert res["pair_kind"] == ocm.OCM_REMOTE_RDMA and res["pair_remote"]  # fixes reference ocm_is_remote bug
+    assert res["pair_rank"] == 1 and res["pair_rsz"] == 2 << 20      # neighbour policy (r+1)%N
+    assert res["far_eq"] and res["win_eq"] and res["off_eq"] and res["read_eq"]
+    assert res["hop1"] and res["hop2"] and res["p2p_eq"]
+    assert res["sig"] == 1 and res["sig2"] == 2
+    assert res["self_rank"] == 0
+    assert res["range_err"]
+    assert res["live"] == 4 and res["live_end"] == 0
+    assert (res["fast"] > 0) == (path == "fast") and (res["slow"] > 0) == (path == "daemon")
+    assert res["remote_pool_used"] >= 2 << 20
+    assert res["double_free_noop"]
+
+
+def test_three_ranks_slow_path_forwarding():
+    """REQ_ALLOC from rank 1 -> placement on rank 0 -> DO_ALLOC on rank 2 -> RELEASE_APP."""
+    with ocm.LocalCluster(3, host_bytes=16 << 20, extra_env={"OCM_NO_GPU": "1"}) as cl:
+        code = r"""
+import json, oncilla_b200 as ocm
+ocm.init()
+a = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 1 << 20)
+b = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 1 << 20, policy=ocm.POLICY_EXPLICIT, rank=0)
+c = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 1 << 20, policy=ocm.POLICY_LEAST_LOADED)
+a.local_tensor()[:] = 7
+a.put(4096)
+ok = int(a.remote_tensor()[:4096].sum()) == 7 * 4096
+used = [ocm.stats(rank=r)["pool_host_used"] for r in range(3)]
+ranks = [a.remote_rank, b.remote_rank, c.remote_rank]
+for x in (a, b, c): x.free()
+import time; time.sleep(0.2)
+after = [ocm.stats(rank=r)["allocs_live"] for r in range(3)]
+ocm.tini()
+print("RESULT " + json.dumps({"ranks": ranks, "ok": ok, "used": used, "after": after}))
+"""
+        out = _ok(run_py(cl, 1, code, env_extra={"OCM_ALLOC_PATH": "daemon"}))
+        res = json.loads(out.split("RESULT ", 1)[1])
+        assert res["ranks"][0] == 2 and res["ranks"][1] == 0
+        assert res["ok"]
+        assert res["used"][2] >= 1 << 20 and res["used"][0] >= 1 << 20
+        assert res["after"] == [0, 0, 0]
+
+
+def test_app_death_is_reclaimed(cluster2):
+    """A crashed application's regions return to the pool (TODO in reference README:68-69)."""
+    code = r"""
+import os, oncilla_b200 as ocm
+ocm.init()
+keep = [ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 4 << 20) for _ in range(3)]
+print("USED", ocm.stats(rank=1)["pool_host_used"], flush=True)
+os._exit(0)   # no free, no tini
+"""
+    out = _ok(run_py(cluster2, 0, code))
+    assert int(out.split("USED ", 1)[1].split()[0]) >= 12 << 20
+    probe = r"""
+import time, oncilla_b200 as ocm
+ocm.init()
+t0 = time.time()
+while time.time() - t0 < 10:
+    s0, s1 = ocm.stats(rank=0), ocm.stats(rank=1)
+    if s0["allocs_live"] == 0 and s1["allocs_live"] == 0 and s1["pool_host_used"] == 0: break
+    time.sleep(0.05)
+print("LIVE", s0["allocs_live"], s1["allocs_live"], s1["pool_host_used"])
+a = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 24 << 20)   # needs the reclaimed space (32 MiB pool)
+print("ZERO", int(a.remote_tensor().sum()))
+a.free(); ocm.tini()
+"""
+    out = _ok(run_py(cluster2, 0, probe))
+    assert "LIVE 0 0 0" in out and "ZERO 0" in out
+
+
+def test_daemon_death_is_detected(cluster2):
+    """Calls fail promptly when a daemon disappears instead of spinning forever (reference src/pmsg.c:134-151)."""
+    code = r"""
+import os, signal, time, json, oncilla_b200 as ocm
+ocm.init()
+a = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 1 << 20)
+os.kill(int(os.environ["VICTIM"]), signal.SIGKILL)
+time.sleep(0.3)
+t0 = time.time()
+try:
+    ocm.stats(rank=0); ok = False
+except ocm.OcmError as e:
+    ok = e.err == 3
+print("RESULT " + json.dumps({"ok": ok, "dt": time.time() - t0}))
+os._exit(0)
+"""
+    victim = cluster2.procs[0].pid
+    out = _ok(run_py(cluster2, 0, code, env_extra={"VICTIM": str(victim)}))
+    res = json.loads(out.split("RESULT ", 1)[1])
+    assert res["ok"] and res["dt"] < 5
+
+
+def test_exhaustion_and_local_fallback():
+    with ocm.LocalCluster(1, host_bytes=4 << 20, extra_env={"OCM_NO_GPU": "1"}) as cl:
+        code = r"""
+import json, oncilla_b200 as ocm
+ocm.init()
+res = {}
+try:
+    ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 64 << 20); res["enomem"] = False
+except ocm.OcmError as e:
+    res["enomem"] = e.err == 2
+big = ocm.alloc(ocm.OCM_LOCAL_HOST, 16 << 20)      # larger than the pool: malloc fallback like the reference
+big.local_tensor()[:] = 1
+res["fallback_ok"] = int(big.local_tensor().sum()) == 16 << 20
+one = ocm.alloc(ocm.OCM_REMOTE_RMA, 4096, 1 << 20)  # single-rank cluster: stays on rank 0
+res["single_rank"] = one.remote_rank
+big.free(); one.free(); ocm.tini()
+print("RESULT " + json.dumps(res))
+"""
+        out = _ok(run_py(cl, 0, code))
+        res = json.loads(out.split("RESULT ", 1)[1])
+        assert res == {"enomem": True, "fallback_ok": True, "single_rank": 0}
+
+
+def test_many_clients_alloc_free(cluster2):
+    """Scaled-down many-client stress (BASELINE.json config 5: 64 apps x 10k; the full size runs in bench/)."""
+    n_apps, iters = 12, 400
+    procs = []
+    for i in range(n_apps):
+        env = cluster2.env(i % 2)
+        env["OCM_ALLOC_PATH"] = "fast" if i % 3 else "daemon"
+        procs.append(subprocess.Popen([str(BIN / "ocm_stress"), str(iters), "65536"], env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.STDOUT, text=True))
+    outs = [p.communicate(timeout=300)[0] for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o
+        assert "pass" in o
+    code = r"""
+import oncilla_b200 as ocm, time
+ocm.init(); time.sleep(0.3)
+print("LIVE", [ocm.stats(rank=r)["allocs_live"] for r in range(2)], [ocm.stats(rank=r)["pool_host_used"] for r in range(2)])
+ocm.tini()
+"""
+    out = _ok(run_py(cluster2, 0, code))
+    assert "LIVE [0, 0] [0, 0]" in out
+
+
+def test_reference_format_nodefile(tmp_path):
+    """A nodefile in the reference's exact 5-column format boots a daemon when OCM_RANK selects the line."""
+    nf = tmp_path / "nodefile"
+    ports = ocm.cluster._free_ports(1)
+    nf.write_text(f"#rank dns ethernet_ip ocm_port rdmacm_port\n0 shiva.cc.gt.atl.ga.us 127.0.0.1 {ports[0]} 67890\n")
+    with ocm.LocalCluster(1, nodefile=str(nf), extra_env={"OCM_NO_GPU": "1", "OCM_HOST_BYTES": "8M"}) as cl:
+        out = _ok(run_app(cl, 0, [BIN / "ocm_test", 1, "1", "1", "1"]))
+        assert "pass" in out
