@@ -1,0 +1,153 @@
+"""`bench.py --impl reference`: run the UNMODIFIED reference (built into baseline/_ref by baseline/Makefile)
+through its own public API for the same metric as bench.py's own arm.
+
+Layout per torchrun rank r (one per GPU): a private UTS+IPC namespace (`unshare --uts --ipc`) with hostname
+``ocmref<r>`` - the reference finds its rank by hostname and has ONE global daemon queue per IPC namespace
+(reference src/nodefile.c:92-103, inc/pmsg.h:24), so several daemons on one host need this - running the
+reference daemon plus `ref_bench`, a timing harness that only calls the reference's ocm_* functions.  The
+nine ib_* symbols come from the loop-back shim (baseline/ib_shim.c).  With one rank the reference itself
+downgrades the remote request to local host memory (reference src/alloc.c:82-83): its N=1 number is a
+pageable cudaMemcpy D2H; with N >= 2 it is cudaMemcpy D2H into the bounce buffer + ib_write to the
+neighbour daemon (reference src/lib.c:643-649).
+"""
+from __future__ import annotations
+
+import json
+import os
+import shutil
+import socket
+import subprocess
+import time
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+REF = HERE / "_ref"
+
+
+def _free_ports(n):
+    socks, ports = [], []
+    for _ in range(n):
+        s = socket.socket()
+        s.bind(("127.0.0.1", 0))
+        socks.append(s)
+        ports.append(s.getsockname()[1])
+    for s in socks:
+        s.close()
+    return ports
+
+
+def unavailable(why: str) -> None:
+    print(json.dumps({"impl": "reference", "unavailable": why}), flush=True)
+
+
+def main(args) -> None:
+    if not (REF / "bin" / "oncillamem").exists() or not (REF / "bin" / "ref_bench").exists():
+        return unavailable("baseline/_ref not built (make -C baseline REF=/root/reference); pip install of the "
+                           "reference is impossible: it has neither setup.py nor pyproject.toml")
+    if shutil.which("unshare") is None:
+        return unavailable("unshare(1) missing: cannot give each reference daemon its own hostname/IPC namespace")
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", str(rank)))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus:
+        return unavailable(f"--gpus {args.gpus} needs torchrun with {args.gpus} processes (WORLD_SIZE={world})")
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("gloo")
+
+    def barrier():
+        if dist:
+            dist.barrier()
+
+    def bcast(obj):
+        if not dist:
+            return obj
+        box = [obj]
+        dist.broadcast_object_list(box, src=0)
+        return box[0]
+
+    tag = os.environ.get("MASTER_PORT", str(os.getpid()))
+    shared = Path(f"/tmp/ocm_ref_{tag}")
+    if rank == 0:
+        shutil.rmtree(shared, ignore_errors=True)
+        shared.mkdir(parents=True)
+        ports = _free_ports(world)
+        lines = ["#rank dns ethernet_ip ocm_port rdmacm_port"]
+        lines += [f"{r} ocmref{r} 127.0.0.1 {ports[r]} 67890" for r in range(world)]
+        (shared / "nodefile").write_text("\n".join(lines) + "\n")
+    barrier()
+    nodefile, go, log = shared / "nodefile", shared / "go", shared / f"daemon{rank}.log"
+    S, K, W = args.size, args.steps, max(args.warmup, 3)
+    script = (f"hostname ocmref{rank} || exit 97; {REF}/bin/oncillamem {nodefile} > {log} 2>&1 & D=$!; "
+              f"for i in $(seq 1 3000); do [ -e {go} ] && break; sleep 0.02; done; "
+              f"{REF}/bin/ref_bench {S} {K} {W} {min(args.alloc_iters, 50)}; RC=$?; "
+              f"kill -INT $D 2>/dev/null; sleep 0.2; kill -KILL $D 2>/dev/null; exit $RC")
+    env = dict(os.environ)
+    env["CUDA_VISIBLE_DEVICES"] = str(local)     # the reference always uses device 0
+    env.pop("OCM_VERBOSE", None)
+
+    def launch():
+        return subprocess.Popen(["unshare", "--uts", "--ipc", "bash", "-c", script], env=env, stdout=subprocess.PIPE,
+                                stderr=subprocess.PIPE, text=True)
+
+    proc = None
+    if rank == 0:
+        proc = launch()            # master first ("start the master first", reference src/mem.c:472)
+        time.sleep(0.5)
+    barrier()
+    if rank != 0:
+        proc = launch()
+    barrier()
+    time.sleep(1.0)                # MSG_ADD_NODE from every rank has reached rank 0
+    barrier()
+    if rank == 0:
+        go.touch()
+    try:
+        out, err = proc.communicate(timeout=900)
+    except subprocess.TimeoutExpired:
+        proc.kill()
+        out, err = proc.communicate()
+    res = None
+    for line in out.splitlines():
+        if line.startswith("{"):
+            try:
+                res = json.loads(line)
+            except json.JSONDecodeError:
+                pass
+    mine = res if (res and "error" not in res and proc.returncode == 0) else {
+        "error": (res or {}).get("error") or f"rc={proc.returncode} out={out[-300:]!r} err={err[-300:]!r}"}
+    gathered = [mine]
+    if dist:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, mine)
+    barrier()
+    if rank == 0:
+        bad = [g for g in gathered if "error" in g]
+        if bad:
+            unavailable("reference run failed: " + str(bad[0]["error"])[:300])
+        else:
+            copy_s = max(g["copy_s"] for g in gathered)
+            e2e_s = max(g["e2e_s"] for g in gathered)
+            out = {
+                "impl": "reference",
+                "metric": "ocm_copy GB/s (GPU alloc -> remote alloc on neighbour rank), aggregate over ranks",
+                "value": round(world * S * K / copy_s / 1e9, 3), "unit": "GB/s", "n_gpus": world, "steps": K,
+                "warmup": W, "ms_per_step": round(copy_s / K * 1e3, 4), "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "bytes (no arithmetic)", "data": "synthetic",
+                "config": {"model": "ocm_copy LOCAL_GPU->REMOTE_RDMA (ib loop-back shim)", "message_bytes": S,
+                           "global_batch": world, "seq_len": S, "parallelism": f"neighbour-put x{world}",
+                           "granted_kind": gathered[0]["granted_kind"], "timing": "host clock around blocking calls"},
+                "e2e": {"value": round(world * S * K / e2e_s / 1e9, 3), "unit": "GB/s", "h2d_bytes_per_step": 0,
+                        "d2h_bytes_per_step": 0, "path": "ocm_copy(LOCAL_HOST -> remote), all on the CPU side"},
+                "gpu_launches": 0,
+                "alloc_p50_us": max(g["alloc_p50_us"] for g in gathered),
+            }
+            if gathered[0].get("put_s"):
+                out["onesided_put_GBps"] = round(world * S * K / max(g["put_s"] for g in gathered) / 1e9, 3)
+                out["onesided_get_GBps"] = round(world * S * K / max(g["get_s"] for g in gathered) / 1e9, 3)
+            print(json.dumps(out), flush=True)
+    if dist:
+        dist.destroy_process_group()

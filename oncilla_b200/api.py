@@ -50,9 +50,10 @@ def _stream_ptr(stream) -> Optional[int]:
     """None -> library stream; a torch.cuda.Stream or raw int -> its cudaStream_t."""
     if stream is None:
         return None
-    if isinstance(stream, int):
-        return stream
-    return int(stream.cuda_stream)
+    h = stream if isinstance(stream, int) else int(stream.cuda_stream)
+    # torch's default stream has handle 0, which the C API reads as "library stream":
+    # name it explicitly (cudaStreamLegacy == 1)
+    return h if h else 1
 
 
 def current_stream_ptr() -> int:

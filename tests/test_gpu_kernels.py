@@ -95,7 +95,8 @@ def test_fill_verify_checksum(nbytes, off):
     assert ops.verify(buf[off:], pat, nbytes) == 0
     buf[off + nbytes // 2] ^= 0xFF
     assert ops.verify(buf[off:], pat, nbytes) == 1
-    want = ocm._native.lib.ocm_oracle_checksum(ctypes.c_void_p(buf.cpu()[off:].data_ptr()), nbytes)
+    host2 = buf.cpu()                            # keep the host copy alive across the C call
+    want = ocm._native.lib.ocm_oracle_checksum(ctypes.c_void_p(host2[off:].data_ptr()), nbytes)
     assert ops.checksum(buf[off:], nbytes) == want
 
 
