@@ -71,6 +71,26 @@ static int get_all(int fd, void *b, size_t n) {
     return 0;
 }
 
+/* Several reference daemons share one network namespace here and every one of them numbers its
+ * per-allocation ports from the same start (reference src/mem.c:38,355-356), so each daemon gets its own
+ * loop-back address, derived from the trailing digits of its hostname: "ocmref3" -> 127.0.1.4. */
+static void shim_ip(char *out, size_t len) {
+    char host[256] = "";
+    size_t n;
+    unsigned v = 0, mul = 1;
+    int digits = 0;
+    gethostname(host, sizeof host - 1);
+    n = strlen(host);
+    while (n > 0 && host[n - 1] >= '0' && host[n - 1] <= '9' && digits < 3) {
+        v += (unsigned)(host[n - 1] - '0') * mul;
+        mul *= 10;
+        --n;
+        ++digits;
+    }
+    if (digits) snprintf(out, len, "127.0.1.%u", (v % 250) + 1);
+    else snprintf(out, len, "127.0.0.1");
+}
+
 int ib_init(void) { return 0; }
 
 ib_t ib_new(struct ib_params *p) {
@@ -119,7 +139,11 @@ static int server_connect(struct ib_alloc *ib) {
     setsockopt(ib->lsock, SOL_SOCKET, SO_REUSEADDR, &one, sizeof one);
     memset(&a, 0, sizeof a);
     a.sin_family = AF_INET;
-    a.sin_addr.s_addr = htonl(INADDR_ANY);
+    {
+        char ip[64];
+        shim_ip(ip, sizeof ip);
+        if (inet_pton(AF_INET, ip, &a.sin_addr) != 1) a.sin_addr.s_addr = htonl(INADDR_ANY);
+    }
     a.sin_port = htons((uint16_t)ib->params.port);   /* the reference truncates its 67980+ ports the same way */
     if (bind(ib->lsock, (struct sockaddr *)&a, sizeof a) || listen(ib->lsock, 1)) return -1;
     ib->sock = accept(ib->lsock, NULL, NULL);        /* blocks until the application connects */
@@ -230,6 +254,6 @@ int ib_poll(ib_t ib) {
 
 int ib_nic_ip(int idx, char *ip_str, size_t len) {
     (void)idx;
-    snprintf(ip_str, len, "127.0.0.1");
+    shim_ip(ip_str, len);
     return 0;
 }

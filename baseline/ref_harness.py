@@ -87,6 +87,7 @@ def main(args) -> None:
               f"kill -INT $D 2>/dev/null; sleep 0.2; kill -KILL $D 2>/dev/null; exit $RC")
     env = dict(os.environ)
     env["CUDA_VISIBLE_DEVICES"] = str(local)     # the reference always uses device 0
+    env["REF_SYNC_DIR"], env["REF_RANK"], env["REF_WORLD"] = str(shared), str(rank), str(world)
     env.pop("OCM_VERBOSE", None)
 
     def launch():

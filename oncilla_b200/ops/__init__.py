@@ -135,3 +135,31 @@ def sort_u64(keys, tmp=None, *, stream=None) -> None:
 
 def launch_count() -> int:
     return int(lib.ocmk_launch_count())
+
+
+def _device_guarded(fn):
+    """Launch on the device of the first CUDA tensor argument (not on whatever device is current)."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(*args, **kw):
+        dev = None
+        for a in list(args) + list(kw.values()):
+            if isinstance(a, (list, tuple)) and a:
+                a = a[0]
+            d = getattr(a, "device", None)
+            if d is not None and getattr(d, "type", None) == "cuda":
+                dev = d
+                break
+        if dev is None:
+            return fn(*args, **kw)
+        import torch
+
+        with torch.cuda.device(dev):
+            return fn(*args, **kw)
+
+    return wrapper
+
+
+for _n in ("copy", "fill", "verify", "checksum", "signal", "strided_copy", "put_replicated", "gups", "sort_u64"):
+    globals()[_n] = _device_guarded(globals()[_n])

@@ -204,10 +204,10 @@ def test_peer_gpu_is_really_remote(gpu_cluster):
 import torch, oncilla_b200 as ocm
 from oncilla_b200 import ops
 ocm.init()
-assert ocm.device() == 1
+assert ocm.device() == 1                        # attached to rank 1 -> GPU 1; torch's current device stays 0 on purpose
 b = ocm.alloc(ocm.OCM_REMOTE_GPU, {n}, {n})     # lands on rank 0 (neighbour of 1): other direction
 ops.fill(b.local_tensor(), 0x55)
-torch.cuda.synchronize()
+torch.cuda.synchronize(1)
 b.put({n}); b.get({n})
 print("BAD", ops.verify(b.local_tensor(), 0x55))
 b.free(); ocm.tini()
