@@ -19,6 +19,10 @@ src = torch.randint(0, 256, (n,), dtype=torch.uint8, device="cuda")
 dst = torch.empty_like(src)
 dst2 = torch.empty_like(src)
 for _ in range(3):
+    if what in ("v32", "all"):
+        ops.copy(dst, src, n)                      # default dispatch: 256-bit vector kernel
+    if what in ("v32dual", "all"):
+        ops.copy(dst, src, n, dst2=dst2)
     if what in ("copy", "all"):
         ops.copy(dst, src, n, mode=1)
     if what in ("dual", "all"):

@@ -138,6 +138,64 @@ __global__ void __launch_bounds__(256) ocm_copy_vec_kernel(CopyArgs a) {
     if (threadIdx.x == 0) finish_and_signal(a.signal, a.ticket);
 }
 
+// 256-bit vector path (LDG.E.ENL2.256 / STG.E.ENL2.256, new on sm_100): the measured winner for pure
+// copies on B200 - it matches cudaMemcpy inside one HBM and over NVLink and has ~2 us less fixed cost
+// than staging through shared memory (profiles/kbench_*.md).  All pointers must be congruent mod 32;
+// up to 31 head bytes and the tail are moved bytewise by the first CTA.
+struct V32 {
+    uint32_t w[8];
+};
+__device__ __forceinline__ V32 ld_v32(const uint8_t *p) {
+    V32 v;
+    asm volatile("ld.global.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(v.w[0]), "=r"(v.w[1]), "=r"(v.w[2]), "=r"(v.w[3]), "=r"(v.w[4]), "=r"(v.w[5]), "=r"(v.w[6]),
+                   "=r"(v.w[7])
+                 : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_v32(uint8_t *p, const V32 &v) {
+    asm volatile("st.global.L1::no_allocate.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v.w[0]), "r"(v.w[1]),
+                 "r"(v.w[2]), "r"(v.w[3]), "r"(v.w[4]), "r"(v.w[5]), "r"(v.w[6]), "r"(v.w[7])
+                 : "memory");
+}
+
+template <bool DUAL>
+__global__ void __launch_bounds__(256) ocm_copy_v32_kernel(CopyArgs a) {
+    uint64_t head = (32 - ((uintptr_t)a.dst & 31)) & 31;
+    if (head > a.bytes) head = a.bytes;
+    const uint64_t n = (a.bytes - head) / 32;
+    const uint8_t *s = a.src + head;
+    uint8_t *d = a.dst + head;
+    uint8_t *d2 = DUAL ? a.dst2 + head : nullptr;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + stride < n; i += 2 * stride) {
+        V32 v0 = ld_v32(s + i * 32), v1 = ld_v32(s + (i + stride) * 32);
+        st_v32(d + i * 32, v0);
+        st_v32(d + (i + stride) * 32, v1);
+        if (DUAL) {
+            st_v32(d2 + i * 32, v0);
+            st_v32(d2 + (i + stride) * 32, v1);
+        }
+    }
+    for (; i < n; i += stride) {
+        V32 v = ld_v32(s + i * 32);
+        st_v32(d + i * 32, v);
+        if (DUAL) st_v32(d2 + i * 32, v);
+    }
+    if (blockIdx.x == 0) {
+        const uint64_t tail0 = head + n * 32;
+        for (uint64_t o = threadIdx.x; o < head + (a.bytes - tail0); o += blockDim.x) {
+            const uint64_t k = o < head ? o : tail0 + (o - head);
+            const uint8_t v = a.src[k];
+            a.dst[k] = v;
+            if (DUAL) a.dst2[k] = v;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) finish_and_signal(a.signal, a.ticket);
+}
+
 __global__ void ocm_signal_kernel(uint64_t *signal) {
     __threadfence_system();
     red_release_sys_add(signal, 1ull);
@@ -213,11 +271,23 @@ cudaError_t launch_copy(void *dst, void *dst2, const void *src, size_t bytes, ui
     const uintptr_t align_or = (uintptr_t)src | (uintptr_t)dst | (uintptr_t)dst2;
     const int sms = num_sms();
 
-    bool bulk = (align_or & 15) == 0 && bytes >= 16;
-    if (t.mode == COPY_VEC) bulk = false;
-    else if (t.mode == COPY_AUTO && bytes < t.bulk_min) bulk = false;
+    // AUTO: the 256-bit vector kernel whenever the pointers are congruent mod 32 (pool blocks always are);
+    // the TMA kernel only on request (OCM_COPY_MODE=bulk / mode=COPY_BULK); narrower vectors otherwise.
+    bool bulk = t.mode == COPY_BULK && (align_or & 15) == 0 && bytes >= 16;
+    const uintptr_t r32 = (uintptr_t)dst & 31;
+    const bool v32 = !bulk && t.mode != COPY_VEC && ((uintptr_t)src & 31) == r32 && (!dst2 || ((uintptr_t)dst2 & 31) == r32);
 
-    if (bulk) {
+    if (v32) {
+        a.tile = 0;
+        a.stages = 0;
+        const uint64_t n32 = bytes / 32;
+        const uint64_t want = (n32 + 511) / 512;           // 2 x 32 B per thread per iteration
+        int cap = t.ctas > 0 ? t.ctas : sms * 4;
+        int ctas = (int)std::min<uint64_t>(std::max<uint64_t>(want, 1), (uint64_t)cap);
+        if (ctas > 1 && signal && !ticket) return cudaErrorInvalidValue;
+        if (dst2) ocm_copy_v32_kernel<true><<<ctas, 256, 0, stream>>>(a);
+        else ocm_copy_v32_kernel<false><<<ctas, 256, 0, stream>>>(a);
+    } else if (bulk) {
         int agents = std::min(std::max(t.agents, 1), kMaxAgents);
         int stages = std::min(std::max(t.stages, 2), kMaxStages);
         size_t tile = ((size_t)std::max(t.tile_bytes, 1024) + 127) & ~(size_t)127;

@@ -10,6 +10,7 @@
 namespace ocmk {
 
 // ---- K1/K2/K3: contiguous put / get / third-party copy ----------------------
+// AUTO picks the 256-bit vector kernel when alignment allows, else VEC; BULK = TMA staging through smem.
 enum CopyMode { COPY_AUTO = 0, COPY_BULK = 1, COPY_VEC = 2 };
 struct CopyTuning {
     int mode = COPY_AUTO;

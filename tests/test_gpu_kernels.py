@@ -19,7 +19,7 @@ def rnd_bytes(n, seed=0):
     return torch.randint(0, 256, (n,), dtype=torch.uint8, device="cuda", generator=g)
 
 
-@pytest.mark.parametrize("mode", [1, 2])  # 1 bulk (TMA), 2 vector
+@pytest.mark.parametrize("mode", [None, 1, 2])  # auto (256-bit vector), 1 bulk (TMA), 2 vector (16 B)
 @pytest.mark.parametrize("nbytes", [16, 4096, 65536 + 16, (1 << 20) + 48, (64 << 20) + 7])
 def test_copy_matches_memcpy(mode, nbytes):
     src = rnd_bytes(nbytes + 64, seed=nbytes)
@@ -41,7 +41,7 @@ def test_copy_alignments(src_off, dst_off):
     assert int(dst[:dst_off].sum()) == 0 and int(dst[dst_off + n:].sum()) == 0
 
 
-@pytest.mark.parametrize("mode", [1, 2])
+@pytest.mark.parametrize("mode", [None, 1, 2])
 def test_copy_two_destinations_and_signal(mode):
     n = (8 << 20) + 32
     src = rnd_bytes(n, seed=3)
