@@ -158,6 +158,7 @@ _sig("ocmk_put_replicated", C.c_int, P(C.c_void_p), C.c_int, C.c_void_p, C.c_siz
 _sig("ocmk_gups", C.c_int, P(C.c_void_p), C.c_int, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p)
 _sig("ocmk_gups_threads", C.c_uint64, C.c_uint64)
 _sig("ocmk_sort_u64", C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p)
+_sig("ocmk_sort_u64_noalloc", C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p)
 _sig("ocmk_launch_count", C.c_uint64)
 # oracles
 _sig("ocm_oracle_copy", None, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t)
