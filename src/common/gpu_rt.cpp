@@ -263,6 +263,23 @@ bool pool_import_ipc(const uint8_t ipc_handle[64], size_t bytes, int owner_dev, 
     return true;
 }
 
+bool pool_grant_access(const PoolMapping *m, int dev, std::string *err) {
+    if (!m->ptr || m->mode != GPU_SHARE_VMM_FD || !drv().ok) {
+        set_err(err, "not a VMM mapping");
+        return false;
+    }
+    CUmemAccessDesc ad = {};
+    ad.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+    ad.location.id = dev;
+    ad.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+    CUresult r = drv().MemSetAccess((CUdeviceptr)m->ptr, m->bytes, &ad, 1);
+    if (r != CUDA_SUCCESS) {
+        set_err(err, "cuMemSetAccess(dev " + std::to_string(dev) + "): " + cu_str(r));
+        return false;
+    }
+    return true;
+}
+
 void pool_release(PoolMapping *m) {
     if (!m->ptr) return;
     if (m->mode == GPU_SHARE_VMM_FD && drv().ok) {

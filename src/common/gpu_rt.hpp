@@ -47,6 +47,8 @@ bool pool_import_fd(int fd, size_t bytes, int owner_dev, int access_dev, PoolMap
 bool pool_import_ipc(const uint8_t ipc_handle[64], size_t bytes, int owner_dev, int access_dev, PoolMapping *out,
                      std::string *err);
 void pool_release(PoolMapping *m);
+// Let one more device of this process access an existing VMM mapping (same virtual address).
+bool pool_grant_access(const PoolMapping *m, int dev, std::string *err);
 
 // Pin + map an existing host range (shared-memory pools, tables) so kernels and
 // async copies can use it.  Idempotent per range.

@@ -242,11 +242,14 @@ __global__ void __launch_bounds__(256) ocm_cast_kernel(CastArgs a) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
             for (uint32_t o = G >> 1; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-            const float scale = amax > 0.f ? __fdiv_rn(amax, 448.0f) : 1.0f;
+            // scale = amax/448 and its reciprocal: two IEEE divisions per thread, then multiplies
+            // (the oracle performs the same operations in the same order, so results match bit for bit)
+            const float scale = amax > 1e-30f ? __fdiv_rn(amax, 448.0f) : 1.0f;   // (near-)zero block: scale 1
+            const float inv = __fdiv_rn(1.0f, scale);
             if (valid) {
                 if ((ch % G) == 0) a.scales[row * a.bpr + ch / G] = scale;
 #pragma unroll
-                for (int i = 0; i < 8; ++i) v[i] = __fdiv_rn(v[i], scale);
+                for (int i = 0; i < 8; ++i) v[i] = __fmul_rn(v[i], inv);
             }
         } else if (dequant && valid) {
             const float scale = a.scales[row * a.bpr + ch / G];
@@ -294,14 +297,15 @@ __global__ void __launch_bounds__(256) ocm_cast_scalar_kernel(CastArgs a) {
         if (quant) {
             float amax = 0.f;
             for (uint64_t e = lo; e < hi; ++e) amax = fmaxf(amax, fabsf(load1(s + e * ss, a.src_dtype)));
-            scale = amax > 0.f ? __fdiv_rn(amax, 448.0f) : 1.0f;
+            scale = amax > 1e-30f ? __fdiv_rn(amax, 448.0f) : 1.0f;
             a.scales[row * a.bpr + b] = scale;
         } else if (dequant) {
             scale = a.scales[row * a.bpr + b];
         }
+        const float inv = quant ? __fdiv_rn(1.0f, scale) : 1.0f;
         for (uint64_t e = lo; e < hi; ++e) {
             float f = load1(s + e * ss, a.src_dtype);
-            if (quant) f = __fdiv_rn(f, scale);
+            if (quant) f = __fmul_rn(f, inv);
             else if (dequant) f = __fmul_rn(f, scale);
             store1(d + e * ds, a.dst_dtype, f);
         }

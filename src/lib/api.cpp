@@ -370,6 +370,7 @@ int ocm_init(void) {
     c.daemon_mq = mq_daemon_name(want_rank);
     const char *ap = getenv("OCM_ALLOC_PATH");
     c.force_slow = ap && (!strcmp(ap, "daemon") || !strcmp(ap, "slow"));
+    if (const char *pm = getenv("OCM_PULL_MIN")) c.pull_min = strtoull(pm, nullptr, 0);
     const char *et = getenv("OCM_INIT_TIMEOUT_MS");
     int timeout_ms = et ? atoi(et) : 5000;
 
@@ -467,6 +468,21 @@ int ocm_tini(void) {
         if (c.tickets) cudaFree(c.tickets);
         c.stream = nullptr;
         c.tickets = nullptr;
+        for (auto &p : c.peer_exec) {
+            if (!p.ok) {
+                p = PeerExec();
+                continue;
+            }
+            for (auto &e : p.ev_in)
+                if (e) cudaEventDestroy((cudaEvent_t)e);
+            DeviceGuard dq(p.dev);
+            cudaStreamSynchronize((cudaStream_t)p.stream);
+            for (auto &e : p.ev_out)
+                if (e) cudaEventDestroy((cudaEvent_t)e);
+            cudaStreamDestroy((cudaStream_t)p.stream);
+            if (p.tickets) cudaFree(p.tickets);
+            p = PeerExec();
+        }
     }
     Message m;
     m.init(MSG_DISCONNECT);

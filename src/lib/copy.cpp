@@ -36,6 +36,114 @@ static int cuda_err(cudaError_t e, const char *what) {
     return OCM_ECUDA;
 }
 
+// ---- pull-mode puts ---------------------------------------------------------------------------
+// SM-issued stores over NVLink top out near 714 GB/s on B200 while SM-issued loads reach ~780 GB/s
+// (profiles/README.md).  For a large put into a peer GPU's pool this process therefore launches the copy
+// kernel ON THE OWNER GPU (it can: all GPUs of the box are visible), which pulls the bytes with loads.
+// Stream order is kept with two events: user stream -> owner-GPU stream -> user stream.
+static std::mutex g_peer_mu;
+
+static PeerExec *get_peer_exec(int dev) {
+    Ctx &c = ctx();
+    if (dev < 0 || dev >= kMaxGpus || dev == c.device) return nullptr;
+    std::lock_guard<std::mutex> g(g_peer_mu);
+    PeerExec &p = c.peer_exec[dev];
+    if (!p.tried) {
+        p.tried = true;
+        p.dev = dev;
+        bool ok = true;
+        {
+            DeviceGuard dg(dev);
+            cudaStream_t s = nullptr;
+            ok = cudaFree(0) == cudaSuccess && cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) == cudaSuccess;
+            p.stream = s;
+            for (int i = 0; ok && i < 16; ++i) {
+                cudaEvent_t e;
+                ok = cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
+                p.ev_out[i] = e;
+            }
+            if (ok) {
+                ok = cudaMalloc((void **)&p.tickets, 16 * sizeof(unsigned)) == cudaSuccess &&
+                     cudaMemset(p.tickets, 0, 16 * sizeof(unsigned)) == cudaSuccess;
+            }
+        }
+        {
+            DeviceGuard dg(c.device);
+            for (int i = 0; ok && i < 16; ++i) {
+                cudaEvent_t e;
+                ok = cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
+                p.ev_in[i] = e;
+            }
+        }
+        if (!ok) {
+            cudaGetLastError();
+            LOGW("cannot drive GPU %d from this process: large puts stay in push mode", dev);
+        }
+        p.ok = ok;
+    }
+    return p.ok ? &p : nullptr;
+}
+
+static bool ensure_access(RankView *v, int dev) {
+    Ctx &c = ctx();
+    if (!v || !v->gpu.ptr) return false;
+    if (dev == c.device || (v->access_mask & (1ull << dev))) return true;
+    std::lock_guard<std::mutex> g(g_peer_mu);
+    std::string err;
+    if (!gpu::pool_grant_access(&v->gpu, dev, &err)) {
+        LOGW("%s", err.c_str());
+        return false;
+    }
+    v->access_mask |= 1ull << dev;
+    return true;
+}
+
+// Returns OCM_EUNSUPPORTED when the transfer does not qualify (caller falls back to push mode).
+static int try_pull_put(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2_off, const Side &src,
+                        uint64_t src_off, uint64_t bytes, uint64_t *signal, cudaStream_t st) {
+    Ctx &c = ctx();
+    if (!c.pull_min || bytes < c.pull_min) return OCM_EUNSUPPORTED;
+    if (src.tier != TIER_GPU || dst.tier != TIER_GPU || src.backing != SIDE_POOL || dst.backing != SIDE_POOL)
+        return OCM_EUNSUPPORTED;
+    if (dst2 && dst2->tier != TIER_GPU) return OCM_EUNSUPPORTED;
+    RankView *dv = get_view(dst.rank, true), *sv = get_view(src.rank, true);
+    if (!dv || !sv || !dv->gpu.ptr || !sv->gpu.ptr) return OCM_EUNSUPPORTED;
+    const int qdev = dv->hdr->gpu_index;
+    if (qdev < 0 || qdev == c.device || sv->hdr->gpu_index != c.device) return OCM_EUNSUPPORTED;
+    if (dv->gpu.mode != GPU_SHARE_VMM_FD || sv->gpu.mode != GPU_SHARE_VMM_FD) return OCM_EUNSUPPORTED;
+    PeerExec *pe = get_peer_exec(qdev);
+    if (!pe || !ensure_access(dv, qdev) || !ensure_access(sv, qdev)) return OCM_EUNSUPPORTED;
+
+    unsigned slot;
+    {
+        std::lock_guard<std::mutex> g(g_peer_mu);
+        slot = pe->cursor++ % 16;
+    }
+    cudaError_t e;
+    {
+        DeviceGuard dg(c.device);
+        e = cudaEventRecord((cudaEvent_t)pe->ev_in[slot], st);
+    }
+    if (e == cudaSuccess) {
+        DeviceGuard dg(qdev);
+        e = cudaStreamWaitEvent((cudaStream_t)pe->stream, (cudaEvent_t)pe->ev_in[slot], 0);
+        if (e == cudaSuccess)
+            e = ocmk::launch_copy((char *)dst.ptr + dst_off, nullptr, (const char *)src.ptr + src_off, bytes, signal,
+                                  pe->tickets + slot, (cudaStream_t)pe->stream, nullptr, &c.kernel_launches);
+        if (e == cudaSuccess) e = cudaEventRecord((cudaEvent_t)pe->ev_out[slot], (cudaStream_t)pe->stream);
+    }
+    if (e == cudaSuccess) {
+        DeviceGuard dg(c.device);
+        if (dst2)   // the window is local: its copy runs here, concurrently with the pull
+            e = ocmk::launch_copy((char *)dst2->ptr + dst2_off, nullptr, (const char *)src.ptr + src_off, bytes, nullptr,
+                                  next_ticket(), st, nullptr, &c.kernel_launches);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(st, (cudaEvent_t)pe->ev_out[slot], 0);
+    }
+    if (e != cudaSuccess) return cuda_err(e, "pull-mode put");
+    c.n_pulled.fetch_add(1, std::memory_order_relaxed);
+    return OCM_OK;
+}
+
 static int single_copy(const Side &dst, uint64_t dst_off, const Side &src, uint64_t src_off, uint64_t bytes,
                        cudaStream_t st, bool *used_stream, uint64_t *signal, bool *signalled) {
     Ctx &c = ctx();
@@ -87,7 +195,13 @@ int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2
     if (c.device < 0) return OCM_ENOGPU;
     DeviceGuard dg(c.device);
     bool signalled = false;
-    int err = OCM_OK;
+    int err = try_pull_put(dst, dst_off, dst2, dst2_off, src, src_off, bytes, signal, st);
+    if (err == OCM_OK) {
+        *used_stream = true;
+        return OCM_OK;
+    }
+    if (err != OCM_EUNSUPPORTED) return err;
+    err = OCM_OK;
 
     // fused path: one kernel reads the source once and feeds every destination
     const bool gpu_dst = dst.tier == TIER_GPU || (dst2 && dst2->tier == TIER_GPU);

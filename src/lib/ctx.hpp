@@ -25,6 +25,18 @@ struct RankView {
     ShmMapping   host_map;
     bool         gpu_tried = false;
     gpu::PoolMapping gpu;       // ptr == nullptr if the rank has no HBM pool or we have no GPU
+    uint64_t     access_mask = 0;   // devices of this process that may touch `gpu` (bit = CUDA ordinal)
+};
+
+// A second GPU this process launches kernels on: the OWNER of a far side, so that a large put runs as
+// loads over NVLink from the destination GPU ("pull") instead of stores from the source GPU ("push").
+struct PeerExec {
+    bool      tried = false, ok = false;
+    int       dev = -1;
+    void     *stream = nullptr;
+    void     *ev_in[16] = {nullptr}, *ev_out[16] = {nullptr};
+    unsigned  cursor = 0;
+    unsigned *tickets = nullptr;
 };
 
 enum SideBacking : uint8_t { SIDE_NONE = 0, SIDE_POOL = 1, SIDE_HEAP = 2, SIDE_CUDAMALLOC = 3, SIDE_USER = 4 };
@@ -83,6 +95,9 @@ struct Ctx {
     std::atomic<uint64_t> n_alloc{0}, n_free{0}, n_fast{0}, n_slow{0}, n_copies{0}, copy_bytes{0};
     unsigned long long kernel_launches = 0;
     std::atomic<uint64_t> bytes_live[TIER_COUNT];
+    PeerExec     peer_exec[kMaxGpus];
+    uint64_t     pull_min = 8ull << 20;   // puts at least this large are pulled by the owner GPU (0: never)
+    std::atomic<uint64_t> n_pulled{0};
 };
 constexpr int kNumTickets = 1024;
 

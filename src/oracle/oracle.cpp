@@ -143,10 +143,11 @@ int ocm_oracle_strided_copy(const struct ocm_oracle_strided *d) {
                         uint64_t lo = b * blk, hi = std::min(elems, lo + blk);
                         float amax = 0.f;
                         for (uint64_t e = lo; e < hi; ++e) amax = fmaxf(amax, fabsf(load_elem(s + e * dsize(sd), sd)));
-                        float scale = amax > 0.f ? amax / 448.0f : 1.0f;
+                        float scale = amax > 1e-30f ? amax / 448.0f : 1.0f;   // (near-)zero block: scale 1
                         d->scales[row * bpr + b] = scale;
+                        const float inv = 1.0f / scale;   // quantise by multiplying with the reciprocal (as the kernel)
                         for (uint64_t e = lo; e < hi; ++e)
-                            t[e] = ocm_oracle_f32_to_e4m3(load_elem(s + e * dsize(sd), sd) / scale);
+                            t[e] = ocm_oracle_f32_to_e4m3(load_elem(s + e * dsize(sd), sd) * inv);
                     }
                 } else if (dequant) {
                     for (uint64_t e = 0; e < elems; ++e) {
