@@ -1,0 +1,113 @@
+#!/usr/bin/env python
+"""Application-level configurations of BASELINE.json on N GPUs (run under torchrun, one rank per GPU):
+
+  config 3  GUPS over pooled HBM: every rank updates its own table striped over ALL ranks' pools
+  config 4  out-of-core sort spanning peer HBM + the pinned host tier (per rank, scaled by --sort-keys)
+  config 5  strided fp8-cast copies into the neighbour's HBM (K4/K5 over NVLink)
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 bench/workloads.py
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import sys
+from pathlib import Path
+
+REPO = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(REPO))
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+import oncilla_b200 as ocm  # noqa: E402
+from oncilla_b200 import ops  # noqa: E402
+from oncilla_b200.cluster import TorchrunCluster  # noqa: E402
+from oncilla_b200.models import gups, sort  # noqa: E402
+
+
+def allmax(x, world):
+    if world == 1:
+        return x
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def allsum(x, world):
+    if world == 1:
+        return x
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gups-words", type=int, default=1 << 28)      # 2 GiB table per rank, striped over all ranks
+    ap.add_argument("--gups-updates", type=int, default=1 << 28)
+    ap.add_argument("--sort-keys", type=int, default=1 << 26)       # 512 MiB of keys per rank
+    ap.add_argument("--sort-chunk", type=int, default=1 << 23)
+    ap.add_argument("--hbm-frac", type=float, default=0.5, help="fraction of the sort's data allowed in peer HBM; rest spills to host")
+    args = ap.parse_args()
+    tc = TorchrunCluster(gpu_bytes=8 << 30, host_bytes=3 << 30)
+    with tc as (rank, world):
+        # ---- config 3 ------------------------------------------------------------------------
+        tc.barrier()
+        g = gups.run(total_words=args.gups_words, n_updates=args.gups_updates, iters=3)
+        tc.barrier()
+        worst = allmax(g["seconds"], world)
+        ok = allsum(1.0 if g["verified"] else 0.0, world) == world
+        if rank == 0:
+            print(json.dumps({"kind": "gups", "n_gpus": world, "table_words_per_rank": args.gups_words,
+                              "updates_per_rank": args.gups_updates, "seconds_max": round(worst, 6),
+                              "GUPS_aggregate": round(world * args.gups_updates / worst / 1e9, 3), "verified": ok}), flush=True)
+        # ---- config 4 ------------------------------------------------------------------------
+        tc.barrier()
+        # half of the runs (and of the output) fit the HBM budget, the rest spills to the pinned host tier
+        s = sort.run(total_keys=args.sort_keys, chunk_keys=args.sort_chunk,
+                     gpu_budget_total=int(args.hbm_frac * args.sort_keys * 8))
+        tc.barrier()
+        worst = allmax(s["seconds"], world)
+        ok = allsum(1.0 if s["ok"] else 0.0, world) == world
+        if rank == 0:
+            print(json.dumps({"kind": "ooc_sort", "n_gpus": world, "keys_per_rank": args.sort_keys,
+                              "bytes_per_rank": args.sort_keys * 8, "seconds_max": round(worst, 4),
+                              "Mkeys_per_s_aggregate": round(world * args.sort_keys / worst / 1e6, 1),
+                              "bytes_in_hbm_rank0": s["bytes_in_hbm"], "bytes_in_host_rank0": s["bytes_in_host"],
+                              "verified": ok}), flush=True)
+        # ---- config 5 (copy part): strided fp32 -> block-scaled fp8 put into the neighbour's HBM ----------
+        rows, elems, pitch = 16384, 4096, 8192
+        src = ocm.alloc(ocm.OCM_LOCAL_GPU, rows * pitch * 4)
+        src.local_tensor(torch.float32).normal_()
+        payload = rows * elems
+        dst = ocm.alloc(ocm.OCM_REMOTE_GPU, 0, payload + rows * (elems // 32) * 4, flags=ocm.ALLOC_NO_WINDOW)
+        st = torch.cuda.current_stream()
+
+        def step():
+            ocm.copy_strided(dst, src, row_bytes=elems * 4, counts=(rows, 1, 1), src_strides=(pitch * 4, 0, 0),
+                             dst_strides=(elems, 0, 0), src_dtype=ocm.DT_F32, dst_dtype=ocm.DT_F8E4M3, scale_block=32,
+                             scale_offset=payload, stream=st)
+
+        for _ in range(3):
+            step()
+        tc.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            step()
+        e1.record()
+        tc.barrier()
+        sec = allmax(e0.elapsed_time(e1) / 1e3 / 10, world)
+        if rank == 0:
+            print(json.dumps({"kind": "strided_fp8_put", "n_gpus": world, "rows": rows, "elems": elems,
+                              "src_bytes": rows * elems * 4, "wire_bytes": payload + rows * (elems // 32) * 4,
+                              "us": round(sec * 1e6, 1),
+                              "src_GBps_aggregate": round(world * rows * elems * 4 / sec / 1e9, 1),
+                              "wire_GBps_per_gpu": round((payload + rows * (elems // 32) * 4) / sec / 1e9, 1)}), flush=True)
+        src.free()
+        dst.free()
+
+
+if __name__ == "__main__":
+    main()

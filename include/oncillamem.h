@@ -132,6 +132,10 @@ int      ocm_remote_rank(ocm_alloc_t a); /* owner rank of the far side, -1 for l
  * (peer HBM or peer pinned DRAM); NULL for local and striped kinds. */
 void    *ocm_remote_ptr(ocm_alloc_t a);
 uint64_t ocm_alloc_id(ocm_alloc_t a);
+/* Multi-slab kinds (OCM_STRIPED_GPU / OCM_REPLICATED_GPU): the slab that lives on `rank`, as mapped into
+ * this process, and the bytes per slab.  Striped: logical offset o lives in slab o / slab_bytes. */
+void    *ocm_slab_ptr(ocm_alloc_t a, int rank);
+uint64_t ocm_slab_bytes(ocm_alloc_t a);
 
 /* ---- stream-ordered copies ------------------------------------------ */
 /* `stream` is a cudaStream_t (NULL = the library's own copy stream).  The

@@ -170,6 +170,16 @@ class Allocation:
             t._ocm_owner = self
         return t if dtype is None else t.view(dtype)
 
+    def slab_tensor(self, rank: int, dtype=None):
+        """Multi-slab kinds: the slab that lives on ``rank`` (peer HBM mapped into this process)."""
+        import torch
+
+        ptr, n = int(lib.ocm_slab_ptr(self.handle, int(rank)) or 0), int(lib.ocm_slab_bytes(self.handle))
+        if not ptr:
+            raise OcmError("allocation has no slab on that rank", 1)
+        t = torch.as_tensor(_CudaView(ptr, n, self), device=f"cuda:{device()}")
+        return t if dtype is None else t.view(dtype)
+
     # ---- signals -------------------------------------------------------------------------
     def signal(self) -> int:
         v = C.c_uint64(0)

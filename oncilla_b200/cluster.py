@@ -48,6 +48,71 @@ def write_nodefile(path: str | Path, n_ranks: int, ports: list[int] | None = Non
     return ports
 
 
+class TorchrunCluster:
+    """Inside a torchrun job (one process per GPU): bring up one daemon per rank and attach this process.
+
+    Rank 0 writes the shared nodefile, every rank starts ITS daemon (master first), then ``ocm.init()``.
+    ``with TorchrunCluster(gpu_bytes=...) as (rank, world): ...``
+    """
+
+    def __init__(self, gpu_bytes: int = 4 << 30, host_bytes: int = 1 << 30, backend: str = "nccl"):
+        self.gpu_bytes, self.host_bytes, self.backend = gpu_bytes, host_bytes, backend
+        self.cl = None
+
+    def barrier(self):
+        import torch
+        import torch.distributed as dist
+
+        if self.world > 1:
+            dist.barrier()
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+
+    def __enter__(self):
+        import torch
+        import torch.distributed as dist
+
+        from . import api
+
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", str(self.rank)))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        torch.cuda.set_device(self.local)
+        if self.world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group(self.backend, device_id=torch.device(f"cuda:{self.local}"))
+        tag = os.environ.get("MASTER_PORT", str(os.getpid()))
+        shared = Path(f"/tmp/ocm_job_{tag}")
+        nodefile = shared / "nodefile"
+        if self.rank == 0:
+            shared.mkdir(parents=True, exist_ok=True)
+            write_nodefile(nodefile, self.world, gpus=list(range(self.world)), gpu_bytes=self.gpu_bytes,
+                           host_bytes=self.host_bytes)
+        self.barrier()
+        self.cl = LocalCluster(self.world, ns=f"job{tag}", nodefile=str(nodefile), ranks=[self.rank])
+        if self.rank == 0:
+            self.cl.start()
+        self.barrier()
+        if self.rank != 0:
+            self.cl.start()
+        self.barrier()
+        self.cl.apply_env(self.rank)
+        os.environ["OCM_DEVICE"] = str(self.local)
+        api.init()
+        return self.rank, self.world
+
+    def __exit__(self, *exc):
+        import torch.distributed as dist
+
+        from . import api
+
+        api.tini()
+        self.barrier()
+        self.cl.stop()
+        if self.world > 1:
+            dist.destroy_process_group()
+
+
 class LocalCluster:
     """N daemons on this host.  Use as a context manager.
 

@@ -25,9 +25,10 @@ from ..parallel import alloc_on
 class _Spill:
     """Far-side storage that prefers peer HBM and falls back to the pinned host tier."""
 
-    def __init__(self, gpu_budget_per_rank: int):
+    def __init__(self, gpu_budget_per_rank: int, gpu_budget_total: int | None = None):
         self.n_ranks = api.num_ranks()
         self.left = [gpu_budget_per_rank] * self.n_ranks
+        self.total_left = gpu_budget_total if gpu_budget_total is not None else 1 << 62
         self.next = 0
         self.allocs = []
 
@@ -35,11 +36,12 @@ class _Spill:
         for _ in range(self.n_ranks):
             r = self.next
             self.next = (self.next + 1) % self.n_ranks
-            if self.left[r] >= nbytes:
+            if self.left[r] >= nbytes and self.total_left >= nbytes:
                 try:
                     a = alloc_on(r, nbytes, gpu=True, flags=N.ALLOC_NO_ZERO)
                     if a.kind == N.OCM_REMOTE_GPU:
                         self.left[r] -= nbytes
+                        self.total_left -= nbytes
                         self.allocs.append(a)
                         return a, "hbm"
                     a.free()
@@ -66,7 +68,7 @@ def _gen(chunk_index: int, n: int, device):
 
 
 def run(total_keys: int = 1 << 24, chunk_keys: int = 1 << 21, gpu_budget_per_rank: int = 1 << 62,
-        check: bool = True) -> dict:
+        check: bool = True, gpu_budget_total: int | None = None) -> dict:
     """Sort ``total_keys`` keys using working buffers of ``chunk_keys`` keys.  Returns timings and placement."""
     import torch
 
@@ -74,8 +76,8 @@ def run(total_keys: int = 1 << 24, chunk_keys: int = 1 << 21, gpu_budget_per_ran
     n_runs = (total_keys + chunk_keys - 1) // chunk_keys
     n_parts = n_runs
     run_bytes = chunk_keys * 8
-    spill = _Spill(gpu_budget_per_rank)
-    out_spill = _Spill(gpu_budget_per_rank)
+    spill = _Spill(gpu_budget_per_rank, gpu_budget_total)
+    out_spill = _Spill(gpu_budget_per_rank, gpu_budget_total)
     tiers = {"hbm": 0, "host": 0}
     t_start = time.time()
     # local working set: one OCM window (GPU) big enough for a run / a gathered partition (2x slack)

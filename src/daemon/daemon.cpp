@@ -635,6 +635,13 @@ void Daemon::finish_alloc(Message &m, int err) {
 int Daemon::do_alloc_local(Message &m) {
     Allocation &a = m.u.alloc;
     if (a.tier >= TIER_COUNT) return OCM_EINVAL;
+    // fault injection for tests: OCM_FAULT_ALLOC_EVERY=N makes every N-th fulfilment fail
+    static const long fault_every = getenv("OCM_FAULT_ALLOC_EVERY") ? atol(getenv("OCM_FAULT_ALLOC_EVERY")) : 0;
+    static long fault_count = 0;
+    if (fault_every > 0 && ++fault_count % fault_every == 0) {
+        LOGW("fault injection: failing allocation %ld", fault_count);
+        return OCM_ENOMEM;
+    }
     BlockRef b;
     int err = pool_alloc(tbl_, (int)a.tier, a.bytes, m.pid, m.rank, &b);
     // blocks waiting to be zeroed still hold their space: give the scrubber a bounded moment

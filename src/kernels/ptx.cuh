@@ -151,7 +151,8 @@ __device__ __forceinline__ void mbar_arrive_remote(uint64_t *bar, uint32_t cta) 
 // Elect the last CTA and publish completion.  Called by one thread per CTA
 // after a CTA-wide barrier that follows the CTA's last store.
 __device__ __forceinline__ void finish_and_signal(uint64_t *signal, unsigned *ticket) {
-    __threadfence_system();
+    if (signal == nullptr) return;   // nobody to notify: kernel completion already orders the bytes
+    asm volatile("fence.acq_rel.sys;" ::: "memory");
     bool last = true;
     if (gridDim.x > 1) {
         if (ticket == nullptr) return; // nobody to notify
@@ -159,8 +160,8 @@ __device__ __forceinline__ void finish_and_signal(uint64_t *signal, unsigned *ti
         last = (t == gridDim.x - 1);
         if (last) atomicExch(ticket, 0u); // ready for the next launch
     }
-    if (last && signal) {
-        __threadfence_system();
+    if (last) {
+        asm volatile("fence.acq_rel.sys;" ::: "memory");
         red_release_sys_add(signal, 1ull);
     }
 }

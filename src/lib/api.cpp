@@ -664,6 +664,12 @@ uint64_t ocm_alloc_id(ocm_alloc_t a) {
     return a->paired && a->stripes.empty() ? a->remote.id : a->local.id;
 }
 
+void *ocm_slab_ptr(ocm_alloc_t a, int rank) {
+    if (!valid_handle(a) || rank < 0 || (size_t)rank >= a->stripes.size()) return nullptr;
+    return a->stripes[rank].ptr;
+}
+uint64_t ocm_slab_bytes(ocm_alloc_t a) { return valid_handle(a) ? a->stripe_bytes : 0; }
+
 int ocm_signal_read(ocm_alloc_t a, uint64_t *value) {
     if (!valid_handle(a) || !value) return -OCM_EINVAL;
     const Side &s = (a->paired && a->remote.valid()) ? a->remote : a->local;

@@ -240,10 +240,76 @@ static void mark_pending(ocm_alloc_t a, void *stream, bool used) {
     if (used && !stream) a->lib_stream_pending.store(true, std::memory_order_relaxed);
 }
 
+// Multi-slab kinds.  STRIPED: the far side is one logical range of N * stripe_bytes, block-distributed over
+// the ranks (the "allocations composed of partitioned distributed allocations" the reference only plans,
+// ref src/lib.c:42-45).  REPLICATED: every rank holds a full copy; a put reaches all of them in one pass
+// (cluster-multicast kernel K6), a get reads the nearest replica.
+static int stripes_xfer(ocm_alloc_t a, bool to_far, const Side &local, uint64_t local_off, uint64_t far_off, uint64_t n,
+                        void *stream, bool *used) {
+    Ctx &c = ctx();
+    const size_t N = a->stripes.size();
+    if (!N || !local.ptr) return OCM_EINVAL;
+    if (local_off + n > local.bytes) return OCM_ERANGE;
+    if (a->kind == OCM_REPLICATED_GPU) {
+        if (far_off + n > a->stripe_bytes) return OCM_ERANGE;
+        if (!to_far) {
+            const Side &near = a->stripes[(size_t)c.rank < N ? (size_t)c.rank : 0];
+            return side_copy(local, local_off, nullptr, 0, near, far_off, n, nullptr, stream, used);
+        }
+        const bool aligned = (((uintptr_t)local.ptr + local_off) | far_off) % 16 == 0;
+        if (N <= 8 && aligned && local.tier == TIER_GPU && c.device >= 0) {
+            void *dsts[8];
+            uint64_t *sigs[8];
+            for (size_t r = 0; r < N; ++r) {
+                dsts[r] = (char *)a->stripes[r].ptr + far_off;
+                sigs[r] = a->stripes[r].rec ? reinterpret_cast<uint64_t *>(&a->stripes[r].rec->signal) : nullptr;
+            }
+            DeviceGuard dg(c.device);
+            cudaError_t e = ocmk::launch_put_replicated(dsts, (int)N, (const char *)local.ptr + local_off, n, sigs,
+                                                        next_ticket(), (cudaStream_t)(stream ? stream : c.stream));
+            ++c.kernel_launches;
+            c.n_copies.fetch_add(1, std::memory_order_relaxed);
+            c.copy_bytes.fetch_add(n * N, std::memory_order_relaxed);
+            *used = true;
+            return cuda_err(e, "replicated put");
+        }
+        for (size_t r = 0; r < N; ++r) {
+            int err = side_copy(a->stripes[r], far_off, nullptr, 0, local, local_off, n, a->stripes[r].rec, stream, used);
+            if (err) return err;
+        }
+        return OCM_OK;
+    }
+    // striped
+    if (far_off + n > a->stripe_bytes * N) return OCM_ERANGE;
+    while (n) {
+        const size_t r = (size_t)(far_off / a->stripe_bytes);
+        const uint64_t in = far_off % a->stripe_bytes;
+        const uint64_t piece = std::min<uint64_t>(n, a->stripe_bytes - in);
+        int err = to_far ? side_copy(a->stripes[r], in, nullptr, 0, local, local_off, piece, a->stripes[r].rec, stream, used)
+                         : side_copy(local, local_off, nullptr, 0, a->stripes[r], in, piece, nullptr, stream, used);
+        if (err) return err;
+        far_off += piece;
+        local_off += piece;
+        n -= piece;
+    }
+    return OCM_OK;
+}
+
 static int do_copy(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p, void *stream, bool *used) {
     if (!valid(dst) || !valid(src) || !p) return OCM_EINVAL;
     if (!p->op_flag) std::swap(dst, src);   // "read": data flows the other way (src/lib.c:510-515)
-    if (!dst->stripes.empty() || !src->stripes.empty()) return OCM_EUNSUPPORTED;
+    if (!dst->stripes.empty() && !src->stripes.empty()) return OCM_EUNSUPPORTED;
+    if (!dst->stripes.empty() || !src->stripes.empty()) {
+        // one hop between a local side and the multi-slab far side: src_offset/dest_offset index source/destination
+        ocm_alloc_t multi = dst->stripes.empty() ? src : dst, other = dst->stripes.empty() ? dst : src;
+        if (far_side(other) || !other->local.valid()) return OCM_EUNSUPPORTED;
+        const bool to_far = multi == dst;
+        int err = stripes_xfer(multi, to_far, other->local, to_far ? p->src_offset : p->dest_offset,
+                               to_far ? p->dest_offset : p->src_offset, p->bytes, stream, used);
+        mark_pending(dst, stream, *used);
+        mark_pending(src, stream, *used);
+        return err;
+    }
     const Side *dfar = far_side(dst), *sfar = far_side(src);
     const uint64_t n = p->bytes;
     int err;
@@ -287,6 +353,12 @@ static int do_copy(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p,
 
 static int do_onesided(ocm_alloc_t a, const struct ocm_params *p, void *stream, bool *used) {
     if (!valid(a) || !p) return OCM_EINVAL;
+    if (!a->stripes.empty()) {
+        if (!a->local.valid() || p->bytes > a->local.bytes) return a->local.valid() ? OCM_ERANGE : OCM_EINVAL;
+        int err = stripes_xfer(a, p->op_flag != 0, a->local, p->src_offset, p->dest_offset, p->bytes, stream, used);
+        mark_pending(a, stream, *used);
+        return err;
+    }
     const Side *far = far_side(a);
     if (!far || !a->local.valid()) {
         LOGW("one-sided copy needs a paired allocation with a window");

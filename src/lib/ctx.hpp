@@ -96,7 +96,11 @@ struct Ctx {
     unsigned long long kernel_launches = 0;
     std::atomic<uint64_t> bytes_live[TIER_COUNT];
     PeerExec     peer_exec[kMaxGpus];
-    uint64_t     pull_min = 8ull << 20;   // puts at least this large are pulled by the owner GPU (0: never)
+    // Puts at least this large are pulled by the owner GPU (0: never, the default).  Measured on 2xB200:
+    // pulling reaches 765 GB/s at 1 GiB where pushing stops at 705, but only while the owner GPU is not
+    // busy with ANOTHER process' kernels - with one application per GPU the two contexts time-slice and
+    // the aggregate halves (profiles/README.md).  Opt in with OCM_PULL_MIN=<bytes> for single-initiator use.
+    uint64_t     pull_min = 0;
     std::atomic<uint64_t> n_pulled{0};
 };
 constexpr int kNumTickets = 1024;

@@ -233,6 +233,34 @@ ocm.tini()
     assert "LIVE [0, 0] [0, 0]" in out
 
 
+def test_fault_injection_keeps_accounting_consistent():
+    """Every 3rd owner-side fulfilment fails (OCM_FAULT_ALLOC_EVERY): errors surface, reservations are returned."""
+    with ocm.LocalCluster(2, host_bytes=16 << 20, extra_env={"OCM_NO_GPU": "1", "OCM_FAULT_ALLOC_EVERY": "3"}) as cl:
+        code = r"""
+import json, time, oncilla_b200 as ocm
+ocm.init()
+ok = fail = 0
+held = []
+for i in range(30):
+    try:
+        held.append(ocm.alloc(ocm.OCM_REMOTE_HOST, 0, 64 << 10, flags=ocm.ALLOC_NO_WINDOW | ocm.ALLOC_SLOW_PATH)); ok += 1
+    except ocm.OcmError as e:
+        assert e.err == 2, e
+        fail += 1
+for a in held: a.free()
+time.sleep(0.3)
+live = [ocm.stats(rank=r)["allocs_live"] for r in range(2)]
+used = [ocm.stats(rank=r)["pool_host_used"] for r in range(2)]
+big = ocm.alloc(ocm.OCM_REMOTE_HOST, 0, 12 << 20, flags=ocm.ALLOC_NO_WINDOW)   # capacity accounting did not leak
+big.free(); ocm.tini()
+print("RESULT " + json.dumps({"ok": ok, "fail": fail, "live": live, "used": used}))
+"""
+        out = _ok(run_py(cl, 0, code))
+        res = json.loads(out.split("RESULT ", 1)[1])
+        assert res["ok"] == 20 and res["fail"] == 10
+        assert res["live"] == [0, 0] and res["used"] == [0, 0]
+
+
 def test_reference_format_nodefile(tmp_path):
     """A nodefile in the reference's exact 5-column format boots a daemon when OCM_RANK selects the line."""
     nf = tmp_path / "nodefile"

@@ -171,6 +171,56 @@ def test_strided_fp8_put_on_allocations(gpu_cluster):
         a.free()
 
 
+def test_striped_and_replicated_kinds(gpu_cluster):
+    N = ocm.num_ranks()
+    n = (6 << 20) + 4096
+    ref = torch.randint(0, 256, (n,), dtype=torch.uint8, device="cuda")
+    # striped: one logical range block-distributed over every rank's pool
+    s = ocm.alloc(ocm.OCM_STRIPED_GPU, n, n)
+    assert s.kind == ocm.OCM_STRIPED_GPU and s.is_remote and s.remote_bytes >= n
+    s.local_tensor().copy_(ref)
+    torch.cuda.synchronize()
+    s.put(n)
+    per = s.remote_bytes // N
+    for r in range(N):                               # every slab holds its block
+        lo, hi = r * per, min(n, (r + 1) * per)
+        if hi > lo:
+            assert torch.equal(s.slab_tensor(r)[: hi - lo], ref[lo:hi])
+    s.local_tensor().zero_()
+    torch.cuda.synchronize()
+    s.get(n)
+    assert torch.equal(s.local_tensor(), ref)
+    if N > 1:                                        # a window that straddles a stripe boundary
+        s.local_tensor()[:8192].fill_(0xEE)
+        torch.cuda.synchronize()
+        s.put(8192, src_offset=0, dest_offset=per - 4096)
+        assert int(s.slab_tensor(0)[per - 4096: per].sum()) == 0xEE * 4096
+        assert int(s.slab_tensor(1)[:4096].sum()) == 0xEE * 4096
+    # replicated: one put lands on every rank (cluster-multicast kernel), get reads the nearest replica
+    rp = ocm.alloc(ocm.OCM_REPLICATED_GPU, n, n)
+    assert rp.remote_bytes == n
+    rp.local_tensor().copy_(ref)
+    torch.cuda.synchronize()
+    rp.put(n)
+    for r in range(N):
+        assert torch.equal(rp.slab_tensor(r)[:n], ref)
+    rp.local_tensor().zero_()
+    torch.cuda.synchronize()
+    rp.get(n)
+    assert torch.equal(rp.local_tensor(), ref)
+    # two-sided copy from a plain GPU allocation into the striped range and back
+    g = ocm.alloc(ocm.OCM_LOCAL_GPU, n)
+    g.local_tensor().copy_(ref.flip(0))
+    torch.cuda.synchronize()
+    ocm.copy(s, g, n)
+    g.local_tensor().zero_()
+    torch.cuda.synchronize()
+    ocm.copy(g, s, n)
+    assert torch.equal(g.local_tensor(), ref.flip(0))
+    for a in (s, rp, g):
+        a.free()
+
+
 def test_native_ocm_test_program_gpu(gpu_cluster):
     for args in (["1", "4", "4", "2"], ["1", "4", "8", "7"], ["2", "4", "4", "7"], ["3", "2", "2", "7"],
                  ["4", "1", "1", "7", "3"]):
