@@ -166,5 +166,8 @@ int main(int argc, char **argv) {
     ocm_free(host);
     ocm_tini();
     touch("free_done", g_rank);
+    /* our daemon is stopped when this program exits, but it may still own another rank's far side:
+     * stay until every rank has released its allocations */
+    for (i = 0; i < g_world; ++i) wait_for("free_done", i, 120.0);
     return 0;
 }

@@ -25,14 +25,23 @@ REF = HERE / "_ref"
 
 
 def _free_ports(n):
-    socks, ports = [], []
-    for _ in range(n):
+    """n free TCP ports BELOW the ephemeral range, so no outgoing connection can grab one before the daemon binds."""
+    import random
+
+    ports = []
+    rng = random.Random(os.getpid() ^ int(time.time() * 1000))
+    while len(ports) < n:
+        p = rng.randrange(10000, 30000)
+        if p in ports or 2400 <= p <= 2600:
+            continue
         s = socket.socket()
-        s.bind(("127.0.0.1", 0))
-        socks.append(s)
-        ports.append(s.getsockname()[1])
-    for s in socks:
-        s.close()
+        try:
+            s.bind(("0.0.0.0", p))
+            ports.append(p)
+        except OSError:
+            pass
+        finally:
+            s.close()
     return ports
 
 
@@ -69,7 +78,19 @@ def main(args) -> None:
         dist.broadcast_object_list(box, src=0)
         return box[0]
 
-    tag = os.environ.get("MASTER_PORT", str(os.getpid()))
+    S, K, W = args.size, args.steps, max(args.warmup, 3)
+    gathered = None
+    for attempt in range(2):       # the reference survives an 8-rank run about two times out of three: retry once
+        gathered = _attempt(args, rank, local, world, dist, barrier, attempt)
+        if not any("error" in g for g in gathered):
+            break
+    _report(rank, world, gathered, S, K, W)
+    if dist:
+        dist.destroy_process_group()
+
+
+def _attempt(args, rank, local, world, dist, barrier, attempt):
+    tag = os.environ.get("MASTER_PORT", str(os.getpid())) + f"_{attempt}"
     shared = Path(f"/tmp/ocm_ref_{tag}")
     if rank == 0:
         shutil.rmtree(shared, ignore_errors=True)
@@ -83,7 +104,9 @@ def main(args) -> None:
     S, K, W = args.size, args.steps, max(args.warmup, 3)
     script = (f"hostname ocmref{rank} || exit 97; {REF}/bin/oncillamem {nodefile} > {log} 2>&1 & D=$!; "
               f"for i in $(seq 1 3000); do [ -e {go} ] && break; sleep 0.02; done; "
-              f"{REF}/bin/ref_bench {S} {K} {W} {min(args.alloc_iters, 50)}; RC=$?; "
+              # alloc-latency loop on rank 0 only: every placement adds a dangling node to the reference's
+              # rank-0 list, the fewer the better for its survival at 8 ranks
+              f"{REF}/bin/ref_bench {S} {K} {W} {min(args.alloc_iters, 20) if rank == 0 else 0}; RC=$?; "
               f"kill -INT $D 2>/dev/null; sleep 0.2; kill -KILL $D 2>/dev/null; exit $RC")
     env = dict(os.environ)
     env["CUDA_VISIBLE_DEVICES"] = str(local)     # the reference always uses device 0
@@ -92,7 +115,7 @@ def main(args) -> None:
 
     def launch():
         return subprocess.Popen(["unshare", "--uts", "--ipc", "bash", "-c", script], env=env, stdout=subprocess.PIPE,
-                                stderr=subprocess.PIPE, text=True)
+                                stderr=subprocess.PIPE, text=True, start_new_session=True)
 
     proc = None
     if rank == 0:
@@ -107,9 +130,13 @@ def main(args) -> None:
     if rank == 0:
         go.touch()
     try:
-        out, err = proc.communicate(timeout=900)
+        out, err = proc.communicate(timeout=int(os.environ.get("OCM_REF_TIMEOUT_S", "75")))
     except subprocess.TimeoutExpired:
-        proc.kill()
+        # the reference blocks forever on a lost peer: never let it hang the caller
+        try:
+            os.killpg(os.getpgid(proc.pid), 9)
+        except OSError:
+            proc.kill()
         out, err = proc.communicate()
     res = None
     for line in out.splitlines():
@@ -125,10 +152,15 @@ def main(args) -> None:
         gathered = [None] * world
         dist.all_gather_object(gathered, mine)
     barrier()
+    return gathered
+
+
+def _report(rank, world, gathered, S, K, W):
     if rank == 0:
         bad = [g for g in gathered if "error" in g]
         if bad:
-            unavailable("reference run failed: " + str(bad[0]["error"])[:300])
+            unavailable(f"reference run failed at {world} rank(s) (its daemons hang or abort on their own list/"
+                        "counter races once several ranks allocate, SURVEY App. B #7/#12): " + str(bad[0]["error"])[:200])
         else:
             copy_s = max(g["copy_s"] for g in gathered)
             e2e_s = max(g["e2e_s"] for g in gathered)
@@ -150,5 +182,3 @@ def main(args) -> None:
                 out["onesided_put_GBps"] = round(world * S * K / max(g["put_s"] for g in gathered) / 1e9, 3)
                 out["onesided_get_GBps"] = round(world * S * K / max(g["get_s"] for g in gathered) / 1e9, 3)
             print(json.dumps(out), flush=True)
-    if dist:
-        dist.destroy_process_group()

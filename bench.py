@@ -116,18 +116,26 @@ def run_ocm(args):
         stream = torch.cuda.current_stream()
 
         # --- device-timed: K x ocm_copy(dst <- src) -------------------------------------------------
-        for _ in range(W):
-            ocm.copy(dst, src, S, stream=stream)
+        # clocks are sampled (nvidia-smi, 100 ms period) from the warm-up to the end of the e2e phase: the
+        # device-timed region alone lasts only a few ms
+        clocks = ClockSampler(local, period_ms=100)
+        clocks.__enter__()
+        t_warm = time.perf_counter()
+        while True:                                   # at least W warm-up copies and ~0.4 s under load
+            for _ in range(W):
+                ocm.copy(dst, src, S, stream=stream)
+            torch.cuda.synchronize()
+            if time.perf_counter() - t_warm > 0.4:
+                break
         barrier(world)
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         launches0 = ops.launch_count()
-        with ClockSampler(local) as clocks:
-            barrier(world)
-            ev0.record()
-            for _ in range(K):
-                ocm.copy(dst, src, S, stream=stream)
-            ev1.record()
-            barrier(world)
+        barrier(world)
+        ev0.record()
+        for _ in range(K):
+            ocm.copy(dst, src, S, stream=stream)
+        ev1.record()
+        barrier(world)
         launches = ops.launch_count() - launches0
         ms = allmax(ev0.elapsed_time(ev1), world)
         value = world * S * K / (ms / 1e3) / 1e9
@@ -159,6 +167,7 @@ def run_ocm(args):
         assert got == sig0 + K
         e2e_s = allmax(t1 - t0, world)
         e2e = world * S * K / e2e_s / 1e9
+        clocks.__exit__(None, None, None)
         ok = ok and ops.verify(dst.remote_tensor(), ((0x1111 + rank) & 0xFFFFFFFFFFFFFFFF), S) == 0
 
         # --- p50 ocm_alloc latency (fast path and daemon path) ---------------------------------------------

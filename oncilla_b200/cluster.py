@@ -20,14 +20,23 @@ from . import _native
 
 
 def _free_ports(n: int) -> list[int]:
-    socks, ports = [], []
-    for _ in range(n):
+    """n free TCP ports below the ephemeral range (an outgoing connection cannot grab one before the daemon binds)."""
+    import random
+
+    ports: list[int] = []
+    rng = random.Random(os.getpid() ^ int(time.time() * 1000))
+    while len(ports) < n:
+        p = rng.randrange(10000, 30000)
+        if p in ports:
+            continue
         s = socket.socket()
-        s.bind(("127.0.0.1", 0))
-        socks.append(s)
-        ports.append(s.getsockname()[1])
-    for s in socks:
-        s.close()
+        try:
+            s.bind(("0.0.0.0", p))
+            ports.append(p)
+        except OSError:
+            pass
+        finally:
+            s.close()
     return ports
 
 

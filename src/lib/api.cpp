@@ -16,6 +16,7 @@
 //     one RC queue pair per allocation, src/rdma_client.c:40-179);
 //   * the defects listed in SURVEY Appendix B (#1-#5) are not reproduced.
 #include "ctx.hpp"
+#include "trace.hpp"
 #include "../common/governor.hpp"
 #include "../common/log.hpp"
 #include "../common/names.hpp"
@@ -504,6 +505,7 @@ int ocm_tini(void) {
 enum ocm_kind ocm_alloc_kind(ocm_alloc_t a) { return valid_handle(a) ? a->kind : (enum ocm_kind)0; }
 
 ocm_alloc_t ocm_alloc_ex(const struct ocm_alloc_params_ex *p) {
+    TraceRange tr_("ocm_alloc");
     Ctx &c = ctx();
     if (!p || !c.inited) {
         set_last_error(c.inited ? OCM_EINVAL : OCM_ENODAEMON);
@@ -603,6 +605,7 @@ ocm_alloc_t ocm_alloc(ocm_alloc_param_t alloc_param) {
 }
 
 int ocm_free(ocm_alloc_t a) {
+    TraceRange tr_("ocm_free");
     Ctx &c = ctx();
     if (!valid_handle(a)) {   // NULL and double frees are rejected (reference derefs first, App. B #2)
         set_last_error(OCM_ESTALE);

@@ -15,6 +15,7 @@
 // the second; when the second hop starts where the first one landed
 // the two hops are fused.
 #include "ctx.hpp"
+#include "trace.hpp"
 #include "../common/log.hpp"
 #include "../kernels/kernels.h"
 #include <cstring>
@@ -406,6 +407,7 @@ static Side user_side(void *p, uint64_t bytes) {
 extern "C" {
 
 int ocm_copy_async(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p, void *stream) {
+    TraceRange tr_("ocm_copy_async");
     bool used = false;
     int err = do_copy(dst, src, p, stream, &used);
     set_last_error(err);
@@ -413,12 +415,14 @@ int ocm_copy_async(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p,
 }
 
 int ocm_copy(ocm_alloc_t dst, ocm_alloc_t src, ocm_param_t p) {
+    TraceRange tr_("ocm_copy");
     bool used = false;
     int err = do_copy(dst, src, p, nullptr, &used);
     return finish_sync(err, used, nullptr);
 }
 
 int ocm_copy_onesided_async(ocm_alloc_t a, const struct ocm_params *p, void *stream) {
+    TraceRange tr_("ocm_copy_onesided_async");
     bool used = false;
     int err = do_onesided(a, p, stream, &used);
     set_last_error(err);
@@ -426,6 +430,7 @@ int ocm_copy_onesided_async(ocm_alloc_t a, const struct ocm_params *p, void *str
 }
 
 int ocm_copy_onesided(ocm_alloc_t a, ocm_param_t p) {
+    TraceRange tr_("ocm_copy_onesided");
     bool used = false;
     int err = do_onesided(a, p, nullptr, &used);
     return finish_sync(err, used, nullptr);
