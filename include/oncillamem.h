@@ -136,6 +136,10 @@ uint64_t ocm_alloc_id(ocm_alloc_t a);
  * this process, and the bytes per slab.  Striped: logical offset o lives in slab o / slab_bytes. */
 void    *ocm_slab_ptr(ocm_alloc_t a, int rank);
 uint64_t ocm_slab_bytes(ocm_alloc_t a);
+/* NVLS: 1 once the daemons have bound the multicast region and this process has mapped it; replicated
+ * allocations made after that are multicast-backed (one multimem.st stream reaches every GPU). */
+int      ocm_multicast_ready(void);
+int      ocm_is_multicast(ocm_alloc_t a);
 
 /* ---- stream-ordered copies ------------------------------------------ */
 /* `stream` is a cudaStream_t (NULL = the library's own copy stream).  The

@@ -41,6 +41,19 @@ def device() -> int:
     return lib.ocm_device()
 
 
+def multicast_ready(wait_s: float = 0.0) -> bool:
+    """True once the NVLS multicast region is bound on every GPU and mapped here (daemons bring it up in ~100 ms)."""
+    import time
+
+    t0 = time.time()
+    while True:
+        if lib.ocm_multicast_ready():
+            return True
+        if time.time() - t0 >= wait_s:
+            return False
+        time.sleep(0.02)
+
+
 def quiet() -> None:
     if lib.ocm_quiet() != 0:
         raise OcmError("ocm_quiet", N.lib.ocm_last_error())
@@ -102,6 +115,10 @@ class Allocation:
     @property
     def is_remote(self) -> bool:
         return bool(lib.ocm_is_remote(self.handle))
+
+    @property
+    def is_multicast(self) -> bool:
+        return bool(lib.ocm_is_multicast(self.handle))
 
     @property
     def remote_rank(self) -> int:

@@ -31,6 +31,12 @@ struct Driver {
     decltype(&cuMemImportFromShareableHandle) MemImport = nullptr;
     decltype(&cuMemGetAllocationGranularity) MemGranularity = nullptr;
     decltype(&cuDeviceGetAttribute) DeviceGetAttribute = nullptr;
+    // multicast entry points are optional (older drivers): mc_ok tells
+    bool mc_ok = false;
+    decltype(&cuMulticastCreate) MulticastCreate = nullptr;
+    decltype(&cuMulticastAddDevice) MulticastAddDevice = nullptr;
+    decltype(&cuMulticastBindMem) MulticastBindMem = nullptr;
+    decltype(&cuMulticastGetGranularity) MulticastGetGranularity = nullptr;
 };
 
 template <typename F> bool load(const char *name, F *fn) {
@@ -56,6 +62,9 @@ Driver &drv() {
                load("cuMemImportFromShareableHandle", &x.MemImport) &&
                load("cuMemGetAllocationGranularity", &x.MemGranularity) &&
                load("cuDeviceGetAttribute", &x.DeviceGetAttribute);
+        x.mc_ok = x.ok && load("cuMulticastCreate", &x.MulticastCreate) &&
+                  load("cuMulticastAddDevice", &x.MulticastAddDevice) && load("cuMulticastBindMem", &x.MulticastBindMem) &&
+                  load("cuMulticastGetGranularity", &x.MulticastGetGranularity);
         return x;
     }();
     return d;
@@ -293,6 +302,116 @@ void pool_release(PoolMapping *m) {
     }
     m->ptr = nullptr;
     m->share_fd = -1;
+}
+
+// ---------------------------------------------------------------- multicast --
+bool mc_supported(int dev) {
+    if (!drv().mc_ok || dev < 0) return false;
+    int v = 0;
+    if (drv().DeviceGetAttribute(&v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dev) != CUDA_SUCCESS) return false;
+    return v != 0;
+}
+
+size_t mc_granularity(int n_devices, size_t bytes, bool recommended) {
+    if (!drv().mc_ok) return 0;
+    CUmulticastObjectProp p = {};
+    p.numDevices = (unsigned)n_devices;
+    p.size = bytes;
+    p.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    size_t g = 0;
+    if (drv().MulticastGetGranularity(&g, &p, recommended ? CU_MULTICAST_GRANULARITY_RECOMMENDED
+                                                           : CU_MULTICAST_GRANULARITY_MINIMUM) != CUDA_SUCCESS)
+        return 0;
+    return g;
+}
+
+bool mc_create(int n_devices, size_t bytes, McObject *out, std::string *err) {
+    if (!drv().mc_ok) {
+        set_err(err, "multicast entry points unavailable");
+        return false;
+    }
+    CUmulticastObjectProp p = {};
+    p.numDevices = (unsigned)n_devices;
+    p.size = bytes;
+    p.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    CUmemGenericAllocationHandle h = 0;
+    CUresult r = drv().MulticastCreate(&h, &p);
+    if (r != CUDA_SUCCESS) {
+        set_err(err, "cuMulticastCreate(" + std::to_string(n_devices) + " devices, " + std::to_string(bytes) + " B): " + cu_str(r));
+        return false;
+    }
+    int fd = -1;
+    r = drv().MemExport(&fd, h, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
+    if (r != CUDA_SUCCESS) {
+        drv().MemRelease(h);
+        set_err(err, "export of the multicast object: " + cu_str(r));
+        return false;
+    }
+    out->handle = (uint64_t)h;
+    out->bytes = bytes;
+    out->fd = fd;
+    return true;
+}
+
+bool mc_import(int fd, size_t bytes, McObject *out, std::string *err) {
+    if (!drv().mc_ok) {
+        set_err(err, "multicast entry points unavailable");
+        return false;
+    }
+    CUmemGenericAllocationHandle h = 0;
+    CUresult r = drv().MemImport(&h, (void *)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+    if (r != CUDA_SUCCESS) {
+        set_err(err, "import of the multicast object: " + cu_str(r));
+        return false;
+    }
+    out->handle = (uint64_t)h;
+    out->bytes = bytes;
+    out->fd = -1;
+    return true;
+}
+
+bool mc_add_device(McObject *mc, int dev, std::string *err) {
+    CUresult r = drv().MulticastAddDevice((CUmemGenericAllocationHandle)mc->handle, dev);
+    if (r != CUDA_SUCCESS) {
+        set_err(err, "cuMulticastAddDevice(" + std::to_string(dev) + "): " + cu_str(r));
+        return false;
+    }
+    return true;
+}
+
+bool mc_bind(McObject *mc, size_t mc_off, const PoolMapping *pool, size_t mem_off, size_t bytes, std::string *err) {
+    if (pool->mode != GPU_SHARE_VMM_FD) {
+        set_err(err, "multicast needs a VMM pool");
+        return false;
+    }
+    CUresult r = drv().MulticastBindMem((CUmemGenericAllocationHandle)mc->handle, mc_off,
+                                        (CUmemGenericAllocationHandle)pool->vmm_handle, mem_off, bytes, 0);
+    if (r != CUDA_SUCCESS) {
+        set_err(err, "cuMulticastBindMem(off " + std::to_string(mem_off) + ", " + std::to_string(bytes) + " B): " + cu_str(r));
+        return false;
+    }
+    return true;
+}
+
+bool mc_map(McObject *mc, int dev, std::string *err) {
+    void *ptr = nullptr;
+    if (!map_handle((CUmemGenericAllocationHandle)mc->handle, mc->bytes, dev, &ptr, err)) return false;
+    mc->va = ptr;
+    mc->va_dev = dev;
+    return true;
+}
+
+void mc_release(McObject *mc) {
+    if (!drv().ok) return;
+    if (mc->va) {
+        drv().MemUnmap((CUdeviceptr)mc->va, mc->bytes);
+        drv().MemAddressFree((CUdeviceptr)mc->va, mc->bytes);
+        mc->va = nullptr;
+    }
+    if (mc->handle) drv().MemRelease((CUmemGenericAllocationHandle)mc->handle);
+    if (mc->fd >= 0) close(mc->fd);
+    mc->handle = 0;
+    mc->fd = -1;
 }
 
 namespace {

@@ -50,6 +50,26 @@ void pool_release(PoolMapping *m);
 // Let one more device of this process access an existing VMM mapping (same virtual address).
 bool pool_grant_access(const PoolMapping *m, int dev, std::string *err);
 
+// ---- NVLS multicast objects (cuMulticast*) ------------------------------------------------------
+// One object spans the same number of bytes on every GPU of the cluster; a store to its virtual address
+// (multimem.st) is replicated by the NVSwitch into the memory each device bound to it.
+struct McObject {
+    uint64_t handle = 0;      // CUmemGenericAllocationHandle of the multicast object
+    size_t   bytes = 0;
+    int      fd = -1;         // creator: exported descriptor
+    void    *va = nullptr;    // mapped multicast address (mc_map)
+    int      va_dev = -1;
+};
+bool   mc_supported(int dev);
+size_t mc_granularity(int n_devices, size_t bytes, bool recommended);
+bool   mc_create(int n_devices, size_t bytes, McObject *out, std::string *err);
+bool   mc_import(int fd, size_t bytes, McObject *out, std::string *err);
+bool   mc_add_device(McObject *mc, int dev, std::string *err);
+// Bind [mem_off, mem_off+bytes) of a VMM pool created by pool_create to [mc_off, mc_off+bytes) of the object.
+bool   mc_bind(McObject *mc, size_t mc_off, const PoolMapping *pool, size_t mem_off, size_t bytes, std::string *err);
+bool   mc_map(McObject *mc, int dev, std::string *err);
+void   mc_release(McObject *mc);
+
 // Pin + map an existing host range (shared-memory pools, tables) so kernels and
 // async copies can use it.  Idempotent per range.
 bool host_register(void *p, size_t bytes, std::string *err);

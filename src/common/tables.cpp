@@ -398,6 +398,19 @@ size_t pool_count_live(TableHeader *h, int tier) {
     return n;
 }
 
+int64_t mc_range_alloc(ClusterTable *c, uint64_t bytes) {
+    if (c->mc_state.load(std::memory_order_acquire) != MC_READY || !bytes) return -1;
+    const uint64_t n = (bytes + kMcGranule - 1) / kMcGranule;
+    if (n > c->mc_n_granules) return -1;
+    uint64_t start = find_run(c->mc_bitmap, 0, c->mc_n_granules, n);
+    return start == UINT64_MAX ? -1 : (int64_t)(start * kMcGranule);
+}
+
+void mc_range_free(ClusterTable *c, uint64_t offset, uint64_t bytes) {
+    const uint64_t n = (bytes + kMcGranule - 1) / kMcGranule;
+    bitmap_clear(c->mc_bitmap, offset / kMcGranule, n);
+}
+
 // ---------------------------------------------------------------- cluster --
 void cluster_format(ClusterTable *c, int n_ranks) {
     c->magic = kTableMagic;

@@ -33,8 +33,11 @@
 namespace ocm {
 
 constexpr uint64_t kTableMagic   = 0x4F434D5441424C45ull; // "OCMTABLE"
-constexpr uint32_t kTableVersion = 3;
+constexpr uint32_t kTableVersion = 4;
 constexpr uint32_t kMaxGranules  = 1u << 18;
+constexpr uint64_t kMcGranule     = 64ull << 10;
+constexpr uint32_t kMcMaxGranules = 1u << 14;     // multicast region <= 1 GiB
+enum McState : uint32_t { MC_NONE = 0, MC_CREATED = 1, MC_READY = 2, MC_FAILED = 3 };
 
 enum RegionState : uint32_t { REGION_FREE = 0, REGION_LIVE = 1, REGION_DIRTY = 2, REGION_SCRUBBING = 3 };
 
@@ -89,6 +92,8 @@ struct TableHeader {
     std::atomic<uint32_t> scrub_enabled;
     std::atomic<uint64_t> next_id;
     std::atomic<uint64_t> heartbeat_ns; // daemon liveness (CLOCK_MONOTONIC)
+    uint64_t mc_tail_offset;           // NVLS: byte offset inside the HBM pool mapping of the multicast slice
+    uint64_t mc_bytes;                 //       its length (0: none)
     PoolDesc pool[TIER_COUNT];
 };
 
@@ -115,7 +120,19 @@ struct ClusterTable {
     std::atomic<uint64_t> total_frees;
     std::atomic<uint64_t> rejected;
     NodeSlot node[kMaxRanks];
+    // NVLS multicast region: the same byte range on every rank's GPU, bound to one multicast object
+    // (daemon/daemon.cpp).  Replicated allocations are carved out of it with the bitmap below.
+    std::atomic<uint32_t> mc_state;      // McState
+    uint32_t mc_n_granules;
+    uint64_t mc_bytes;
+    std::atomic<uint32_t> mc_added;      // daemons that added their device
+    std::atomic<uint32_t> mc_bound;      // daemons that bound their slice
+    std::atomic<uint64_t> mc_bitmap[kMcMaxGranules / 64];
 };
+
+// Sub-allocation inside the multicast region (any process).  Returns the byte offset or -1.
+int64_t mc_range_alloc(ClusterTable *c, uint64_t bytes);
+void    mc_range_free(ClusterTable *c, uint64_t offset, uint64_t bytes);
 
 uint64_t default_granule(uint64_t pool_bytes, Tier tier);
 inline std::atomic<uint64_t> *table_bitmap(TableHeader *h, int tier) {

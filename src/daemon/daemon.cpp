@@ -41,6 +41,9 @@ Daemon::~Daemon() {
     sock_close(ep_);
     if (box_.is_open()) box_.close(true);
     if (tbl_) tbl_->ready.store(0);
+    if (cluster_) cluster_->mc_state.store(MC_NONE);
+    if (mc_.handle) gpu::mc_release(&mc_);
+    if (cluster_peer_map_.base) shm_close(&cluster_peer_map_, false);
     if (gpu_pool_.ptr) {
         if (scrub_stream_) cudaStreamDestroy((cudaStream_t)scrub_stream_);
         gpu::pool_release(&gpu_pool_);
@@ -102,11 +105,27 @@ int Daemon::setup_pools() {
     // GPU pool first: VMM rounds the size up, the table must describe the real size.
     uint8_t ipc_handle[64] = {0};
     if (gpu_ >= 0 && gpu_bytes) {
-        if (!gpu::pool_create(gpu_, gpu_bytes, 0, &gpu_pool_, ipc_handle, &err)) {
+        // NVLS: with several ranks a tail of the pool is set aside and later bound to one multicast object
+        uint64_t mc_want = 0;
+        if (n_ranks_ >= 2 && gpu::mc_supported(gpu_)) {
+            mc_want = env_size("OCM_MC_BYTES", 256ull << 20);
+            size_t g = gpu::mc_granularity(n_ranks_, mc_want, false);
+            if (!g) g = 2 << 20;
+            mc_want = std::min<uint64_t>((mc_want + g - 1) / g * g, (uint64_t)kMcMaxGranules * kMcGranule);
+        }
+        const size_t vg = gpu::vmm_granularity(gpu_);
+        gpu_bytes = (gpu_bytes + vg - 1) / vg * vg;
+        if (!gpu::pool_create(gpu_, gpu_bytes + mc_want, 0, &gpu_pool_, ipc_handle, &err)) {
             LOGE("GPU pool: %s", err.c_str());
             return -ENOMEM;
         }
-        gpu_bytes = gpu_pool_.bytes;
+        if (mc_want && gpu_pool_.mode == GPU_SHARE_VMM_FD && gpu_pool_.bytes >= gpu_bytes + mc_want) {
+            mc_bytes_ = mc_want;
+            mc_tail_off_ = gpu_pool_.bytes - mc_want;
+            gpu_bytes = mc_tail_off_;
+        } else {
+            gpu_bytes = gpu_pool_.bytes;
+        }
         cudaStream_t s;
         if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) == cudaSuccess) scrub_stream_ = s;
         // fresh pools start zeroed (remote buffers are zero-filled in the reference, src/alloc.c:171)
@@ -125,6 +144,8 @@ int Daemon::setup_pools() {
     tbl_->gpu_index = gpu_;
     tbl_->gpu_share_mode = gpu_pool_.ptr ? gpu_pool_.mode : GPU_SHARE_NONE;
     memcpy(tbl_->cuda_ipc_handle, ipc_handle, 64);
+    tbl_->mc_tail_offset = mc_tail_off_;
+    tbl_->mc_bytes = mc_bytes_;
     if (gpu_ >= 0) gpu::get_uuid(gpu_, tbl_->gpu_uuid);
     if (getenv("OCM_NO_SCRUB")) tbl_->scrub_enabled.store(0);
 
@@ -223,6 +244,18 @@ int Daemon::init() {
         }
         cluster_ = static_cast<ClusterTable *>(cluster_map_.base);
         cluster_format(cluster_, n_ranks_);
+        if (mc_bytes_) {
+            if (gpu::mc_create(n_ranks_, mc_bytes_, &mc_, &err)) {
+                cluster_->mc_bytes = mc_bytes_;
+                cluster_->mc_n_granules = (uint32_t)(mc_bytes_ / kMcGranule);
+                cluster_->mc_state.store(MC_CREATED, std::memory_order_release);
+                LOGI("multicast object: %llu bytes over %d devices", (unsigned long long)mc_bytes_, n_ranks_);
+            } else {
+                LOGW("NVLS multicast unavailable: %s", err.c_str());
+                cluster_->mc_state.store(MC_FAILED, std::memory_order_release);
+                mc_bytes_ = 0;
+            }
+        }
     }
     scrubber_ = std::thread([this] { scrub_loop(); });
     join_deadline_ns_ = now_ns() + (uint64_t)opt_.join_timeout_ms * 1000000ull;
@@ -724,6 +757,84 @@ void Daemon::fill_stats(StatsPayload *s) {
     s->scrubbed_bytes = scrubbed_bytes_.load();
 }
 
+// ------------------------------------------------------------ NVLS bring-up --
+ClusterTable *Daemon::shared_cluster() {
+    if (cluster_) return cluster_;
+    if (!cluster_peer_map_.base) {
+        std::string err;
+        if (!shm_open_existing(shm_cluster_name(), &cluster_peer_map_, &err)) return nullptr;
+    }
+    auto *ct = static_cast<ClusterTable *>(cluster_peer_map_.base);
+    if (cluster_peer_map_.bytes < sizeof(ClusterTable) || ct->magic != kTableMagic || ct->version != kTableVersion)
+        return nullptr;
+    return ct;
+}
+
+// Every device must be added to the multicast object before any rank binds memory, so the daemons
+// advance in lock step through two counters in the cluster table:
+//   add own device -> mc_added++ ... all added -> bind own pool tail -> mc_bound++ ... all bound -> READY
+void Daemon::mc_step() {
+    if (mc_done_ || !mc_bytes_ || !joined_) return;
+    ClusterTable *ct = shared_cluster();
+    if (!ct) return;
+    const uint32_t st = ct->mc_state.load(std::memory_order_acquire);
+    if (st == MC_FAILED || st == MC_NONE) {
+        if (st == MC_FAILED || now_ns() > join_deadline_ns_) mc_done_ = true;   // rank 0 has no multicast object
+        return;
+    }
+    std::string err;
+    if (!mc_added_) {
+        if (ct->mc_bytes != mc_bytes_) {
+            LOGW("multicast size mismatch (rank 0: %llu, here: %llu): set the same OCM_MC_BYTES everywhere",
+                 (unsigned long long)ct->mc_bytes, (unsigned long long)mc_bytes_);
+            ct->mc_state.store(MC_FAILED, std::memory_order_release);
+            mc_done_ = true;
+            return;
+        }
+        if (rank_ != 0) {
+            UdsReply rp;
+            int fd = -1;
+            if (!uds_fetch(uds_name(0), UDS_GET_MULTICAST, gpu_, &rp, &fd) || rp.err || fd < 0) {
+                if (fd >= 0) close(fd);
+                return;   // rank 0 not serving yet: next tick
+            }
+            bool ok = gpu::mc_import(fd, rp.bytes, &mc_, &err);
+            close(fd);
+            if (!ok) {
+                LOGW("%s", err.c_str());
+                ct->mc_state.store(MC_FAILED, std::memory_order_release);
+                mc_done_ = true;
+                return;
+            }
+        }
+        if (!gpu::mc_add_device(&mc_, gpu_, &err)) {
+            LOGW("%s", err.c_str());
+            ct->mc_state.store(MC_FAILED, std::memory_order_release);
+            mc_done_ = true;
+            return;
+        }
+        mc_added_ = true;
+        ct->mc_added.fetch_add(1, std::memory_order_acq_rel);
+    }
+    if (!mc_bound_ && ct->mc_added.load(std::memory_order_acquire) == (uint32_t)n_ranks_) {
+        if (!gpu::mc_bind(&mc_, 0, &gpu_pool_, mc_tail_off_, mc_bytes_, &err)) {
+            LOGW("%s", err.c_str());
+            ct->mc_state.store(MC_FAILED, std::memory_order_release);
+            mc_done_ = true;
+            return;
+        }
+        mc_bound_ = true;
+        ct->mc_bound.fetch_add(1, std::memory_order_acq_rel);
+    }
+    if (mc_bound_ && ct->mc_bound.load(std::memory_order_acquire) == (uint32_t)n_ranks_) {
+        if (rank_ == 0) {
+            ct->mc_state.store(MC_READY, std::memory_order_release);
+            LOGI("NVLS multicast region ready: %llu bytes on %d GPUs", (unsigned long long)mc_bytes_, n_ranks_);
+        }
+        mc_done_ = true;
+    }
+}
+
 // ------------------------------------------------------- fd server (UDS) ----
 void Daemon::on_uds_accept() {
     for (;;) {
@@ -743,6 +854,16 @@ void Daemon::on_uds_accept() {
             rp.mode = gpu_pool_.ptr ? gpu_pool_.mode : GPU_SHARE_NONE;
             if (!gpu_pool_.ptr) rp.err = OCM_ENOGPU;
             else if (gpu_pool_.mode == GPU_SHARE_VMM_FD) pass = gpu_pool_.share_fd;
+        } else if (rq.what == UDS_GET_MULTICAST) {
+            // rank 0 hands its multicast object to the other daemons and to applications
+            if (rank_ == 0 && mc_.fd >= 0) {
+                rp.bytes = mc_.bytes;
+                rp.owner_dev = gpu_;
+                rp.aux = cluster_ ? cluster_->mc_state.load() : 0;
+                pass = mc_.fd;
+            } else {
+                rp.err = OCM_EUNSUPPORTED;
+            }
         } else {
             rp.err = OCM_EINVAL;
         }
@@ -816,6 +937,7 @@ void Daemon::on_timer() {
             ++it;
         }
     }
+    mc_step();
     if (now - last_reclaim_ns_ > 250ull * 1000000ull) {
         last_reclaim_ns_ = now;
         reclaim_dead();

@@ -85,6 +85,8 @@ class Daemon {
     void close_peer(int fd);
     void scrub_loop();
     void reclaim_dead();
+    void mc_step();                           // NVLS multicast bring-up state machine (timer driven)
+    ClusterTable *shared_cluster();           // rank 0: own table; others: lazily mapped
     uint32_t next_seq() { return ++seq_ ? seq_ : ++seq_; }
 
     DaemonOptions opt_;
@@ -110,6 +112,11 @@ class Daemon {
     // counters
     std::atomic<uint64_t> msgs_in_{0}, msgs_out_{0}, reclaimed_{0}, scrubbed_bytes_{0};
     void *scrub_stream_ = nullptr;
+    // NVLS multicast: the tail of the HBM pool (mc_bytes_ at mc_tail_off_) is bound to rank 0's object
+    gpu::McObject mc_;
+    uint64_t mc_bytes_ = 0, mc_tail_off_ = 0;
+    bool mc_added_ = false, mc_bound_ = false, mc_done_ = false;
+    ShmMapping cluster_peer_map_;
 };
 
 uint64_t now_ns();

@@ -22,6 +22,7 @@
 #include "../common/names.hpp"
 #include "../daemon/uds_proto.hpp"
 #include "../ipc/sock.hpp"
+#include "../kernels/kernels.h"
 #include <cerrno>
 #include <cstring>
 #include <cuda_runtime.h>
@@ -350,6 +351,49 @@ static int alloc_local_side(int tier, uint64_t bytes, uint32_t flags, Side *out)
     return OCM_OK;
 }
 
+// Map rank 0's NVLS multicast object into this process (once).  True when stores to c.mc.va reach every GPU.
+static bool ensure_mc() {
+    Ctx &c = ctx();
+    if (c.mc.va) return true;
+    if (c.device < 0 || !c.cluster || c.cluster->mc_state.load(std::memory_order_acquire) != MC_READY) return false;
+    std::lock_guard<std::mutex> g(c.mq_mu);
+    if (c.mc.va) return true;
+    if (c.mc_tried) return false;
+    c.mc_tried = true;
+    UdsReply rp;
+    int fd = -1;
+    if (!uds_fetch(uds_name(0), UDS_GET_MULTICAST, c.device, &rp, &fd) || rp.err || fd < 0) {
+        if (fd >= 0) close(fd);
+        LOGW("rank 0 did not hand out the multicast object");
+        return false;
+    }
+    std::string err;
+    DeviceGuard dg(c.device);
+    bool ok = gpu::mc_import(fd, rp.bytes, &c.mc, &err) && gpu::mc_map(&c.mc, c.device, &err);
+    close(fd);
+    if (!ok) {
+        LOGW("multicast mapping failed: %s", err.c_str());
+        gpu::mc_release(&c.mc);
+        return false;
+    }
+    return true;
+}
+
+// Release a multicast-backed replicated allocation: zero every replica, then give the range back.
+static void release_mc(lib_alloc *a) {
+    Ctx &c = ctx();
+    if (c.device >= 0 && c.stream) {
+        DeviceGuard dg(c.device);
+        for (auto &s : a->stripes)
+            if (s.ptr) ocmk::launch_fill(s.ptr, a->stripe_bytes, 0, (cudaStream_t)c.stream);
+        cudaStreamSynchronize((cudaStream_t)c.stream);
+    }
+    mc_range_free(c.cluster, a->mc_offset, a->stripe_bytes);
+    c.bytes_live[TIER_GPU].fetch_sub(a->stripe_bytes, std::memory_order_relaxed);
+    for (auto &s : a->stripes) s = Side();
+    a->mc = false;
+}
+
 static bool valid_handle(ocm_alloc_t a) { return a && a->magic == kAllocMagic; }
 
 } // namespace ocm
@@ -492,6 +536,12 @@ int ocm_tini(void) {
     if (c.box.send(c.daemon_mq, &m, 1000)) ret = -1;
     c.box.detach(c.daemon_mq);
     c.box.close(true);
+    if (c.mc.handle) {
+        DeviceGuard dg(c.device);
+        gpu::mc_release(&c.mc);
+    }
+    c.mc = gpu::McObject();
+    c.mc_tried = false;
     drop_views();
     if (c.cluster_map.base) shm_close(&c.cluster_map, false);
     c.cluster = nullptr;
@@ -518,6 +568,9 @@ ocm_alloc_t ocm_alloc_ex(const struct ocm_alloc_params_ex *p) {
     a->kind = kind;
     a->paired = false;
     a->stripe_bytes = 0;
+    a->mc = false;
+    a->mc_offset = 0;
+    a->mc_ptr = nullptr;
     a->lib_stream_pending.store(false);
     int err = OCM_OK;
 
@@ -560,15 +613,43 @@ ocm_alloc_t ocm_alloc_ex(const struct ocm_alloc_params_ex *p) {
         per = (per + 255) & ~255ull;
         a->stripe_bytes = per;
         a->stripes.resize(N);
-        for (int r = 0; r < N && !err; ++r)
+        // replicated: prefer the NVLS multicast region (one range, same offset on every GPU)
+        if (kind == OCM_REPLICATED_GPU && ensure_mc()) {
+            int64_t off = mc_range_alloc(c.cluster, per);
+            bool ok = off >= 0;
+            for (int r = 0; r < N && ok; ++r) {
+                RankView *v = get_view(r, true);
+                ok = v && v->gpu.ptr && v->hdr->mc_bytes >= (uint64_t)off + per;
+                if (!ok) break;
+                Side &s = a->stripes[r];
+                s.backing = SIDE_MC;
+                s.tier = TIER_GPU;
+                s.rank = r;
+                s.offset = v->hdr->mc_tail_offset + (uint64_t)off;
+                s.bytes = per;
+                s.ptr = (char *)v->gpu.ptr + s.offset;
+            }
+            if (ok) {
+                a->mc = true;
+                a->mc_offset = (uint64_t)off;
+                a->mc_ptr = (char *)c.mc.va + off;
+                c.bytes_live[TIER_GPU].fetch_add(per, std::memory_order_relaxed);
+            } else {
+                if (off >= 0) mc_range_free(c.cluster, (uint64_t)off, per);
+                for (auto &s : a->stripes) s = Side();
+            }
+        }
+        for (int r = 0; r < N && !err && !a->mc; ++r)
             err = alloc_side(ALLOC_MEM_REMOTE_GPU, per, OCM_POLICY_EXPLICIT, r, flags, &a->stripes[r]);
         for (int r = 0; r < N && !err; ++r)
             if (a->stripes[r].tier != TIER_GPU) err = OCM_ENOGPU;
         if (!err && !(flags & OCM_ALLOC_NO_WINDOW) && p->base.local_alloc_bytes)
             err = alloc_local_side(TIER_GPU, p->base.local_alloc_bytes, flags, &a->local);
-        if (err)
+        if (err) {
+            if (a->mc) release_mc(a);
             for (auto &s : a->stripes)
                 if (s.valid()) release_side(s);
+        }
         break;
     }
     default:
@@ -628,6 +709,7 @@ int ocm_free(ocm_alloc_t a) {
         int e2 = release_side(a->remote);
         if (!err) err = e2;
     }
+    if (a->mc) release_mc(a);
     for (auto &s : a->stripes)
         if (s.valid()) {
             int e2 = release_side(s);
@@ -672,6 +754,9 @@ void *ocm_slab_ptr(ocm_alloc_t a, int rank) {
     return a->stripes[rank].ptr;
 }
 uint64_t ocm_slab_bytes(ocm_alloc_t a) { return valid_handle(a) ? a->stripe_bytes : 0; }
+
+int ocm_multicast_ready(void) { return ctx().inited && ensure_mc() ? 1 : 0; }
+int ocm_is_multicast(ocm_alloc_t a) { return valid_handle(a) && a->mc ? 1 : 0; }
 
 int ocm_signal_read(ocm_alloc_t a, uint64_t *value) {
     if (!valid_handle(a) || !value) return -OCM_EINVAL;

@@ -258,6 +258,17 @@ static int stripes_xfer(ocm_alloc_t a, bool to_far, const Side &local, uint64_t 
             return side_copy(local, local_off, nullptr, 0, near, far_off, n, nullptr, stream, used);
         }
         const bool aligned = (((uintptr_t)local.ptr + local_off) | far_off) % 16 == 0;
+        if (a->mc && aligned && n % 16 == 0 && local.tier == TIER_GPU && c.device >= 0) {
+            // NVLS: one multimem.st stream, the switch replicates it into every GPU's slice
+            DeviceGuard dg(c.device);
+            cudaError_t e = ocmk::launch_put_multimem((char *)a->mc_ptr + far_off, (const char *)local.ptr + local_off, n,
+                                                      nullptr, next_ticket(), (cudaStream_t)(stream ? stream : c.stream));
+            ++c.kernel_launches;
+            c.n_copies.fetch_add(1, std::memory_order_relaxed);
+            c.copy_bytes.fetch_add(n * N, std::memory_order_relaxed);
+            *used = true;
+            return cuda_err(e, "multimem put");
+        }
         if (N <= 8 && aligned && local.tier == TIER_GPU && c.device >= 0) {
             void *dsts[8];
             uint64_t *sigs[8];

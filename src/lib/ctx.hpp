@@ -39,7 +39,8 @@ struct PeerExec {
     unsigned *tickets = nullptr;
 };
 
-enum SideBacking : uint8_t { SIDE_NONE = 0, SIDE_POOL = 1, SIDE_HEAP = 2, SIDE_CUDAMALLOC = 3, SIDE_USER = 4 };
+enum SideBacking : uint8_t { SIDE_NONE = 0, SIDE_POOL = 1, SIDE_HEAP = 2, SIDE_CUDAMALLOC = 3, SIDE_USER = 4,
+                             SIDE_MC = 5 /* replica inside the NVLS multicast region */ };
 
 // One contiguous piece of memory addressable from this process.
 struct Side {
@@ -68,6 +69,9 @@ struct lib_alloc {
     ocm::Side     remote;        // pairs: the far side
     std::vector<ocm::Side> stripes;   // striped / replicated kinds: one per rank
     uint64_t      stripe_bytes;
+    bool          mc;                 // replicated through the NVLS multicast region
+    uint64_t      mc_offset;          // offset of this allocation inside the region
+    void         *mc_ptr;             // its multicast virtual address
     std::atomic<bool> lib_stream_pending;
 };
 
@@ -96,6 +100,8 @@ struct Ctx {
     unsigned long long kernel_launches = 0;
     std::atomic<uint64_t> bytes_live[TIER_COUNT];
     PeerExec     peer_exec[kMaxGpus];
+    gpu::McObject mc;            // rank 0's multicast object mapped for our device
+    bool         mc_tried = false;
     // Puts at least this large are pulled by the owner GPU (0: never, the default).  Measured on 2xB200:
     // pulling reaches 765 GB/s at 1 GiB where pushing stops at 705, but only while the owner GPU is not
     // busy with ANOTHER process' kernels - with one application per GPU the two contexts time-slice and

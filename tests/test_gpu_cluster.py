@@ -221,6 +221,48 @@ def test_striped_and_replicated_kinds(gpu_cluster):
         a.free()
 
 
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="NVLS multicast needs two GPUs")
+def test_nvls_multicast_replicated_put(gpu_cluster):
+    """OCM_REPLICATED_GPU backed by the NVLS multicast region: one multimem.st stream lands on every GPU."""
+    from oncilla_b200 import api
+
+    if not api.multicast_ready(wait_s=10.0):
+        pytest.skip("NVLS multicast not available on this box (daemons fell back to per-rank slabs)")
+    N = ocm.num_ranks()
+    n = (5 << 20) + 64
+    ref = torch.randint(0, 256, (n,), dtype=torch.uint8, device="cuda")
+    a = ocm.alloc(ocm.OCM_REPLICATED_GPU, n, n)
+    b = ocm.alloc(ocm.OCM_REPLICATED_GPU, 4096, 4096)      # a second range in the same region
+    assert a.is_multicast and b.is_multicast
+    for r in range(N):
+        assert int(a.slab_tensor(r)[:n].sum()) == 0          # the region starts zeroed
+    a.local_tensor().copy_(ref)
+    torch.cuda.synchronize()
+    before = ops.launch_count()
+    a.put(n)
+    assert ops.launch_count() == before + 1                  # one kernel for all replicas
+    for r in range(N):
+        assert torch.equal(a.slab_tensor(r)[:n], ref)
+    assert int(b.slab_tensor(N - 1).sum()) == 0              # neighbours untouched
+    # offsets and an unaligned tail fall back to per-replica stores but stay correct
+    a.local_tensor()[:1000].fill_(7)
+    torch.cuda.synchronize()
+    a.put(1000, src_offset=0, dest_offset=8192)
+    for r in range(N):
+        assert int(a.slab_tensor(r)[8192:9192].sum()) == 7000
+    a.local_tensor().zero_()
+    torch.cuda.synchronize()
+    a.get(n)
+    assert torch.equal(a.local_tensor()[:8192], ref[:8192])
+    a.free()
+    c = ocm.alloc(ocm.OCM_REPLICATED_GPU, n, n)              # the range is reusable and was scrubbed
+    assert c.is_multicast
+    for r in range(N):
+        assert int(c.slab_tensor(r)[:n].sum()) == 0
+    c.free()
+    b.free()
+
+
 def test_native_ocm_test_program_gpu(gpu_cluster):
     for args in (["1", "4", "4", "2"], ["1", "4", "8", "7"], ["2", "4", "4", "7"], ["3", "2", "2", "7"],
                  ["4", "1", "1", "7", "3"]):
