@@ -107,6 +107,45 @@ def main():
                               "wire_GBps_per_gpu": round((payload + rows * (elems // 32) * 4) / sec / 1e9, 1)}), flush=True)
         src.free()
         dst.free()
+        # ---- replicated put (K6): one source -> every GPU; rank 0 alone, then all ranks at once ------------
+        from oncilla_b200 import api as _api
+
+        nrep = 64 << 20
+        ready = _api.multicast_ready(wait_s=5.0) if world > 1 else False
+        rep = ocm.alloc(ocm.OCM_REPLICATED_GPU, nrep, nrep)
+        slabs = [rep.slab_tensor(r) for r in range(world)]
+        win = rep.local_tensor()
+        ops.fill(win, 0x1234)
+        torch.cuda.synchronize()
+
+        def timeit(fn, everyone):
+            tc.barrier()
+            if everyone or rank == 0:
+                for _ in range(3):
+                    fn()
+                torch.cuda.synchronize()
+            tc.barrier()
+            e0.record()
+            if everyone or rank == 0:
+                for _ in range(10):
+                    fn()
+            e1.record()
+            torch.cuda.synchronize()
+            tc.barrier()
+            return allmax(e0.elapsed_time(e1) / 1e3 / 10, world)
+
+        rows_out = {}
+        for everyone in (False, True):
+            tag = "all_ranks" if everyone else "rank0_only"
+            rows_out[tag] = {
+                "api_put_us": round(timeit(lambda: rep.put(nrep, stream=st), everyone) * 1e6, 1),
+                "cluster_kernel_us": round(timeit(lambda: ops.put_replicated(slabs[:8], win, nrep), everyone) * 1e6, 1),
+                "unicast_loop_us": round(timeit(lambda: [ops.copy(s, win, nrep) for s in slabs], everyone) * 1e6, 1),
+            }
+        if rank == 0:
+            print(json.dumps({"kind": "replicated_put", "n_gpus": world, "bytes": nrep, "nvls": bool(rep.is_multicast),
+                              "multicast_ready": ready, **rows_out}), flush=True)
+        rep.free()
 
 
 if __name__ == "__main__":
