@@ -13,8 +13,12 @@
 //    source once.  Source and destination are generic addresses: local HBM,
 //    peer HBM over NVLink, or pinned host memory.  No SM registers touch the
 //    payload.
-//  * vector path: 16-byte LDG/STG grid-stride loop for small or oddly aligned
-//    transfers (lower latency than a trip through shared memory).
+//  * 256-bit vector path (default): 32 bytes per thread per access with the
+//    sm_100 LDG/STG.256, optional second destination.  Measured faster than the
+//    bulk path for pure copies (no shared-memory round trip), see
+//    profiles/README.md; the bulk path is selected with COPY_BULK.
+//  * narrow vector path: 16/8/4/1-byte LDG/STG grid-stride loop for transfers
+//    whose pointers are not congruent mod 32.
 //
 // Completion: the last CTA to finish (elected through a device-local ticket
 // word) adds 1 to the destination's signal word with release semantics at
