@@ -7,9 +7,11 @@
 //   vec16       our 16-byte vector kernel
 //   vec32       experimental 32-byte (256-bit LDG/STG) vector kernel
 #include "kernels/kernels.h"
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <string>
 #include <vector>
 
@@ -123,6 +125,27 @@ int main(int argc, char **argv) {
     cudaStream_t st;
     CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
 
+    {
+        // library baseline for ocm_alloc: what the reference's GPU tier calls per allocation (ref src/lib.c:240,365)
+        for (size_t bytes : {(size_t)(64 << 10), (size_t)(1 << 20), (size_t)(64 << 20), (size_t)(1 << 30)}) {
+            std::vector<double> am, af;
+            for (int i = 0; i < 200; ++i) {
+                void *p = nullptr;
+                struct timespec t0, t1, t2;
+                clock_gettime(CLOCK_MONOTONIC, &t0);
+                CK(cudaMalloc(&p, bytes));
+                clock_gettime(CLOCK_MONOTONIC, &t1);
+                CK(cudaFree(p));
+                clock_gettime(CLOCK_MONOTONIC, &t2);
+                am.push_back((t1.tv_sec - t0.tv_sec) * 1e6 + (t1.tv_nsec - t0.tv_nsec) * 1e-3);
+                af.push_back((t2.tv_sec - t1.tv_sec) * 1e6 + (t2.tv_nsec - t1.tv_nsec) * 1e-3);
+            }
+            std::sort(am.begin(), am.end());
+            std::sort(af.begin(), af.end());
+            printf("{\"kind\": \"cudamalloc_baseline\", \"bytes\": %zu, \"malloc_p50_us\": %.2f, \"free_p50_us\": %.2f}\n", bytes,
+                   am[am.size() / 2], af[af.size() / 2]);
+        }
+    }
     std::vector<Variant> vars = {
         {"memcpy", 0, 0, 0, 0, 0},
         {"auto", 4, 0, 0, 0, 0},
@@ -150,6 +173,25 @@ int main(int argc, char **argv) {
     } else {
         dirs.push_back({"local", b0, a0});
     }
+    // synchronous small-message latency (host clock around enqueue + stream sync): the shape of the
+    // reference's own BW test, which calls a blocking ocm_copy_onesided per message
+    for (auto &d : dirs)
+        for (size_t n : {(size_t)64, (size_t)4096, (size_t)65536, (size_t)(1 << 20)})
+            for (int which = 0; which < 2; ++which) {
+                std::vector<double> us;
+                for (int i = 0; i < 220; ++i) {
+                    struct timespec t0, t1;
+                    clock_gettime(CLOCK_MONOTONIC, &t0);
+                    if (which == 0) CK(cudaMemcpyAsync(d.dst, d.src, n, cudaMemcpyDefault, st));
+                    else CK(ocmk::launch_copy(d.dst, nullptr, d.src, n, nullptr, ticket, st, nullptr));
+                    CK(cudaStreamSynchronize(st));
+                    clock_gettime(CLOCK_MONOTONIC, &t1);
+                    if (i >= 20) us.push_back((t1.tv_sec - t0.tv_sec) * 1e6 + (t1.tv_nsec - t0.tv_nsec) * 1e-3);
+                }
+                std::sort(us.begin(), us.end());
+                printf("{\"kind\": \"sync_latency\", \"dir\": \"%s\", \"bytes\": %zu, \"engine\": \"%s\", \"p50_us\": %.2f, \"p99_us\": %.2f}\n",
+                       d.name, n, which ? "ours" : "memcpy", us[us.size() / 2], us[us.size() * 99 / 100]);
+            }
     for (auto &d : dirs)
         for (size_t n : sizes)
             for (auto &v : vars) {
