@@ -43,6 +43,8 @@ struct CopyArgs {
     uint32_t       stages;
     uint64_t      *signal;
     unsigned      *ticket;
+    uint64_t      *done_flag;     // optional host-visible completion word
+    uint64_t       done_value;
 };
 
 __global__ void __launch_bounds__(kMaxAgents * 32, 1) ocm_copy_bulk_kernel(CopyArgs a) {
@@ -107,7 +109,7 @@ __global__ void __launch_bounds__(kMaxAgents * 32, 1) ocm_copy_bulk_kernel(CopyA
         if (a.dst2) a.dst2[o] = v;
     }
     __syncthreads();
-    if (threadIdx.x == 0) finish_and_signal(a.signal, a.ticket);
+    if (threadIdx.x == 0) finish_and_signal(a.signal, a.ticket, a.done_flag, a.done_value);
 }
 
 // Vector path.  V = access width in bytes (16, 8, 4 or 1): the widest power of
@@ -139,7 +141,7 @@ __global__ void __launch_bounds__(256) ocm_copy_vec_kernel(CopyArgs a) {
         if (a.dst2) a.dst2[done + threadIdx.x] = v;
     }
     __syncthreads();
-    if (threadIdx.x == 0) finish_and_signal(a.signal, a.ticket);
+    if (threadIdx.x == 0) finish_and_signal(a.signal, a.ticket, a.done_flag, a.done_value);
 }
 
 // 256-bit vector path (LDG.E.ENL2.256 / STG.E.ENL2.256, new on sm_100): the measured winner for pure
@@ -197,7 +199,7 @@ __global__ void __launch_bounds__(256) ocm_copy_v32_kernel(CopyArgs a) {
         }
     }
     __syncthreads();
-    if (threadIdx.x == 0) finish_and_signal(a.signal, a.ticket);
+    if (threadIdx.x == 0) finish_and_signal(a.signal, a.ticket, a.done_flag, a.done_value);
 }
 
 __global__ void ocm_signal_kernel(uint64_t *signal) {
@@ -256,7 +258,8 @@ static cudaError_t ensure_bulk_smem(size_t bytes) {
 }
 
 cudaError_t launch_copy(void *dst, void *dst2, const void *src, size_t bytes, uint64_t *signal, unsigned *ticket,
-                        cudaStream_t stream, const CopyTuning *tuning, unsigned long long *launches) {
+                        cudaStream_t stream, const CopyTuning *tuning, unsigned long long *launches,
+                        const CopyNotify *notify) {
     if (bytes == 0) {
         if (signal) {
             ocm_signal_kernel<<<1, 1, 0, stream>>>(signal);
@@ -272,6 +275,8 @@ cudaError_t launch_copy(void *dst, void *dst2, const void *src, size_t bytes, ui
     a.bytes = bytes;
     a.signal = signal;
     a.ticket = ticket;
+    a.done_flag = notify ? notify->flag : nullptr;
+    a.done_value = notify ? notify->value : 0;
     const uintptr_t align_or = (uintptr_t)src | (uintptr_t)dst | (uintptr_t)dst2;
     const int sms = num_sms();
 

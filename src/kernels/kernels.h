@@ -29,8 +29,15 @@ const CopyTuning &default_copy_tuning();
 // ticket: zero-initialised device-local word used to elect the last CTA
 // (required when signal != nullptr and more than one CTA runs).
 // *launches (optional) is incremented by the number of kernels enqueued.
+// notify (optional): a host-visible word that receives `value` (release.sys) once the last byte is visible,
+// so that a blocked host thread can spin on it instead of synchronising the stream.
+struct CopyNotify {
+    uint64_t *flag;
+    uint64_t  value;
+};
 cudaError_t launch_copy(void *dst, void *dst2, const void *src, size_t bytes, uint64_t *signal, unsigned *ticket,
-                        cudaStream_t stream, const CopyTuning *tuning = nullptr, unsigned long long *launches = nullptr);
+                        cudaStream_t stream, const CopyTuning *tuning = nullptr, unsigned long long *launches = nullptr,
+                        const CopyNotify *notify = nullptr);
 
 // ---- K9: fill / verify / checksum --------------------------------------------
 cudaError_t launch_fill(void *dst, size_t bytes, uint64_t pattern, cudaStream_t stream);

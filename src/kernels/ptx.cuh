@@ -150,8 +150,11 @@ __device__ __forceinline__ void mbar_arrive_remote(uint64_t *bar, uint32_t cta) 
 
 // Elect the last CTA and publish completion.  Called by one thread per CTA
 // after a CTA-wide barrier that follows the CTA's last store.
-__device__ __forceinline__ void finish_and_signal(uint64_t *signal, unsigned *ticket) {
-    if (signal == nullptr) return;   // nobody to notify: kernel completion already orders the bytes
+// `done_flag` (optional) is a host-visible word that receives `done_value` (release, system scope) at the same
+// point: a blocked host thread can spin on it instead of paying kernel tear-down + stream synchronisation.
+__device__ __forceinline__ void finish_and_signal(uint64_t *signal, unsigned *ticket, uint64_t *done_flag = nullptr,
+                                                  uint64_t done_value = 0) {
+    if (signal == nullptr && done_flag == nullptr) return;   // nobody to notify: kernel completion orders the bytes
     asm volatile("fence.acq_rel.sys;" ::: "memory");
     bool last = true;
     if (gridDim.x > 1) {
@@ -162,7 +165,8 @@ __device__ __forceinline__ void finish_and_signal(uint64_t *signal, unsigned *ti
     }
     if (last) {
         asm volatile("fence.acq_rel.sys;" ::: "memory");
-        red_release_sys_add(signal, 1ull);
+        if (signal) red_release_sys_add(signal, 1ull);
+        if (done_flag) st_release_sys(done_flag, done_value);
     }
 }
 

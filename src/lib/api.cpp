@@ -468,6 +468,15 @@ int ocm_init(void) {
                 if (cudaMalloc((void **)&c.tickets, kNumTickets * sizeof(unsigned)) == cudaSuccess)
                     cudaMemset(c.tickets, 0, kNumTickets * sizeof(unsigned));
                 else c.tickets = nullptr;
+                void *hw = nullptr;
+                if (!getenv("OCM_NO_SPIN_SYNC") &&
+                    cudaHostAlloc(&hw, 64, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
+                    memset(hw, 0, 64);
+                    c.done_word = static_cast<uint64_t *>(hw);
+                    c.done_seq.store(0);
+                } else {
+                    cudaGetLastError();
+                }
             } else {
                 cudaGetLastError();
             }
@@ -511,6 +520,8 @@ int ocm_tini(void) {
             cudaStreamDestroy((cudaStream_t)c.stream);
         }
         if (c.tickets) cudaFree(c.tickets);
+        if (c.done_word) cudaFreeHost(c.done_word);
+        c.done_word = nullptr;
         c.stream = nullptr;
         c.tickets = nullptr;
         for (auto &p : c.peer_exec) {

@@ -30,6 +30,26 @@ static bool kernel_addressable(const Side &s) {
     return s.backing == SIDE_POOL; // pool host memory is pinned + mapped in this process
 }
 
+// Blocking calls on the library stream: the kernel itself tells a host-visible word when its last byte is
+// visible, and the caller spins on that word instead of paying kernel tear-down + cudaStreamSynchronize
+// (~4 us of a ~13 us small put).  Only used when the whole call was exactly one kernel launch.
+struct SyncNotify {
+    bool armed = false;
+    uint64_t value = 0;
+    int gpu_ops = 0;        // kernels / async memcpys enqueued by the current call
+    int notified = 0;       // ... of which carry the completion word
+    ocmk::CopyNotify cn{nullptr, 0};
+};
+static thread_local SyncNotify t_sn;
+
+static const ocmk::CopyNotify *note_kernel() {
+    ++t_sn.gpu_ops;
+    if (!t_sn.armed) return nullptr;
+    ++t_sn.notified;
+    return &t_sn.cn;
+}
+static void note_other_gpu_op(int n = 1) { t_sn.gpu_ops += n; }
+
 static int cuda_err(cudaError_t e, const char *what) {
     if (e == cudaSuccess) return OCM_OK;
     LOGE("%s: %s", what, cudaGetErrorString(e));
@@ -162,10 +182,12 @@ static int single_copy(const Side &dst, uint64_t dst_off, const Side &src, uint6
     *used_stream = true;
     if (dst.tier == TIER_GPU && src.tier == TIER_GPU) {
         *signalled = signal != nullptr;
-        return cuda_err(ocmk::launch_copy(d, nullptr, s, bytes, signal, next_ticket(), st, nullptr, &c.kernel_launches),
+        return cuda_err(ocmk::launch_copy(d, nullptr, s, bytes, signal, next_ticket(), st, nullptr, &c.kernel_launches,
+                                          note_kernel()),
                         "copy kernel");
     }
     // host tier <-> GPU: copy engine (H1)
+    note_other_gpu_op();
     return cuda_err(cudaMemcpyAsync(d, s, bytes, dst.tier == TIER_GPU ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost, st),
                     "cudaMemcpyAsync");
 }
@@ -199,6 +221,7 @@ int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2
     int err = try_pull_put(dst, dst_off, dst2, dst2_off, src, src_off, bytes, signal, st);
     if (err == OCM_OK) {
         *used_stream = true;
+        note_other_gpu_op(2);
         return OCM_OK;
     }
     if (err != OCM_EUNSUPPORTED) return err;
@@ -213,7 +236,7 @@ int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2
         *used_stream = true;
         err = cuda_err(ocmk::launch_copy((char *)dst.ptr + dst_off, dst2 ? (char *)dst2->ptr + dst2_off : nullptr,
                                          (const char *)src.ptr + src_off, bytes, signal, next_ticket(), st, nullptr,
-                                         &c.kernel_launches),
+                                         &c.kernel_launches, note_kernel()),
                        "copy kernel");
         signalled = signal != nullptr;
     } else {
@@ -224,6 +247,7 @@ int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2
     if (!err && signal && !signalled) {
         if (*used_stream) {
             err = cuda_err(ocmk::launch_signal(signal, st), "signal kernel");
+            note_other_gpu_op();
             ++c.kernel_launches;
         } else {
             signal_rec->signal.fetch_add(1, std::memory_order_release);
@@ -264,6 +288,7 @@ static int stripes_xfer(ocm_alloc_t a, bool to_far, const Side &local, uint64_t 
             cudaError_t e = ocmk::launch_put_multimem((char *)a->mc_ptr + far_off, (const char *)local.ptr + local_off, n,
                                                       nullptr, next_ticket(), (cudaStream_t)(stream ? stream : c.stream));
             ++c.kernel_launches;
+            note_other_gpu_op();
             c.n_copies.fetch_add(1, std::memory_order_relaxed);
             c.copy_bytes.fetch_add(n * N, std::memory_order_relaxed);
             *used = true;
@@ -280,6 +305,7 @@ static int stripes_xfer(ocm_alloc_t a, bool to_far, const Side &local, uint64_t 
             cudaError_t e = ocmk::launch_put_replicated(dsts, (int)N, (const char *)local.ptr + local_off, n, sigs,
                                                         next_ticket(), (cudaStream_t)(stream ? stream : c.stream));
             ++c.kernel_launches;
+            note_other_gpu_op();
             c.n_copies.fetch_add(1, std::memory_order_relaxed);
             c.copy_bytes.fetch_add(n * N, std::memory_order_relaxed);
             *used = true;
@@ -384,13 +410,46 @@ static int do_onesided(ocm_alloc_t a, const struct ocm_params *p, void *stream, 
     return err;
 }
 
+// Arm the completion word for the blocking call that follows on this thread.
+static void arm_sync_notify() {
+    Ctx &c = ctx();
+    t_sn = SyncNotify();
+    if (!c.done_word || c.device < 0) return;
+    t_sn.armed = true;
+    t_sn.value = c.done_seq.fetch_add(1, std::memory_order_relaxed) + 1;
+    t_sn.cn.flag = c.done_word;
+    t_sn.cn.value = t_sn.value;
+}
+
 static int finish_sync(int err, bool used, void *stream) {
     Ctx &c = ctx();
     if (used && c.device >= 0) {
-        DeviceGuard dg(c.device);
-        cudaError_t e = cudaStreamSynchronize((cudaStream_t)(stream ? stream : c.stream));
-        if (e != cudaSuccess && !err) err = cuda_err(e, "stream sync");
+        bool done = false;
+        if (!err && !stream && t_sn.armed && t_sn.gpu_ops == 1 && t_sn.notified == 1) {
+            // exactly one kernel: wait for its completion word (bounded, then fall back to the stream)
+            volatile uint64_t *w = c.done_word;
+            struct timespec t0, t1;
+            clock_gettime(CLOCK_MONOTONIC, &t0);
+            for (unsigned spin = 0; !done; ++spin) {
+                if (*w >= t_sn.value) {
+                    done = true;
+                    break;
+                }
+                if ((spin & 255) == 255) {
+                    clock_gettime(CLOCK_MONOTONIC, &t1);
+                    if ((t1.tv_sec - t0.tv_sec) * 1000000000ll + (t1.tv_nsec - t0.tv_nsec) > 2000000ll) break;   // 2 ms
+                }
+                __builtin_ia32_pause();
+            }
+            std::atomic_thread_fence(std::memory_order_acquire);
+        }
+        if (!done) {
+            DeviceGuard dg(c.device);
+            cudaError_t e = cudaStreamSynchronize((cudaStream_t)(stream ? stream : c.stream));
+            if (e != cudaSuccess && !err) err = cuda_err(e, "stream sync");
+        }
     }
+    t_sn = SyncNotify();
     set_last_error(err);
     return err ? -1 : 0;
 }
@@ -428,6 +487,7 @@ int ocm_copy_async(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p,
 int ocm_copy(ocm_alloc_t dst, ocm_alloc_t src, ocm_param_t p) {
     TraceRange tr_("ocm_copy");
     bool used = false;
+    arm_sync_notify();
     int err = do_copy(dst, src, p, nullptr, &used);
     return finish_sync(err, used, nullptr);
 }
@@ -443,6 +503,7 @@ int ocm_copy_onesided_async(ocm_alloc_t a, const struct ocm_params *p, void *str
 int ocm_copy_onesided(ocm_alloc_t a, ocm_param_t p) {
     TraceRange tr_("ocm_copy_onesided");
     bool used = false;
+    arm_sync_notify();
     int err = do_onesided(a, p, nullptr, &used);
     return finish_sync(err, used, nullptr);
 }

@@ -100,6 +100,8 @@ struct Ctx {
     unsigned long long kernel_launches = 0;
     std::atomic<uint64_t> bytes_live[TIER_COUNT];
     PeerExec     peer_exec[kMaxGpus];
+    uint64_t    *done_word = nullptr;   // pinned, device-visible: kernels of blocking calls report completion here
+    std::atomic<uint64_t> done_seq{0};
     gpu::McObject mc;            // rank 0's multicast object mapped for our device
     bool         mc_tried = false;
     // Puts at least this large are pulled by the owner GPU (0: never, the default).  Measured on 2xB200:
