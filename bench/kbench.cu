@@ -54,6 +54,45 @@ __global__ void __launch_bounds__(256) vec32_kernel(const uint8_t *s, uint8_t *d
     }
 }
 
+// experimental dual-destination variants (window + far side inside one HBM): unroll depth and store policy
+template <int U, int POLICY>   // POLICY 0: L1::no_allocate, 1: .cs (streaming), 2: plain
+__global__ void __launch_bounds__(256) dual_kernel(const uint8_t *s, uint8_t *d, uint8_t *d2, uint64_t bytes) {
+    const uint64_t n = bytes / 32;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    auto ld = [&](uint64_t k, uint32_t *a) {
+        asm volatile("ld.global.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]), "=r"(a[4]), "=r"(a[5]), "=r"(a[6]), "=r"(a[7])
+                     : "l"(s + k * 32));
+    };
+    auto st = [&](uint8_t *base, uint64_t k, const uint32_t *a) {
+        if (POLICY == 0)
+            asm volatile("st.global.L1::no_allocate.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(base + k * 32), "r"(a[0]),
+                         "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]) : "memory");
+        else if (POLICY == 1)
+            asm volatile("st.global.cs.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(base + k * 32), "r"(a[0]), "r"(a[1]),
+                         "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]) : "memory");
+        else
+            asm volatile("st.global.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(base + k * 32), "r"(a[0]), "r"(a[1]),
+                         "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]) : "memory");
+    };
+    for (; i + (U - 1) * stride < n; i += U * stride) {
+        uint32_t v[U][8];
+#pragma unroll
+        for (int u = 0; u < U; ++u) ld(i + u * stride, v[u]);
+#pragma unroll
+        for (int u = 0; u < U; ++u) st(d, i + u * stride, v[u]);
+#pragma unroll
+        for (int u = 0; u < U; ++u) st(d2, i + u * stride, v[u]);
+    }
+    for (; i < n; i += stride) {
+        uint32_t v[8];
+        ld(i, v);
+        st(d, i, v);
+        st(d2, i, v);
+    }
+}
+
 struct Variant {
     std::string name;
     int mode;   // 0 memcpy, 1 bulk, 2 vec16, 3 vec32
@@ -145,6 +184,45 @@ int main(int argc, char **argv) {
             printf("{\"kind\": \"cudamalloc_baseline\", \"bytes\": %zu, \"malloc_p50_us\": %.2f, \"free_p50_us\": %.2f}\n", bytes,
                    am[am.size() / 2], af[af.size() / 2]);
         }
+    }
+    if (argc > 1 && !strcmp(argv[1], "dual")) {
+        // window + far side inside one HBM (bench.py at N=1): product kernel vs experimental variants
+        uint8_t *c0;
+        CK(cudaMalloc(&c0, maxn));
+        const size_t n = 256ull << 20;
+        auto time_it = [&](const char *name, auto &&launch) {
+            for (int i = 0; i < 3; ++i) launch();
+            CK(cudaStreamSynchronize(st));
+            cudaEvent_t e0, e1;
+            CK(cudaEventCreate(&e0));
+            CK(cudaEventCreate(&e1));
+            CK(cudaEventRecord(e0, st));
+            for (int i = 0; i < 20; ++i) launch();
+            CK(cudaEventRecord(e1, st));
+            CK(cudaStreamSynchronize(st));
+            float ms = 0;
+            CK(cudaEventElapsedTime(&ms, e0, e1));
+            printf("{\"kind\": \"dual\", \"bytes\": %zu, \"variant\": \"%s\", \"us\": %.1f, \"GBps\": %.1f, \"hbm_traffic_GBps\": %.1f}\n", n,
+                   name, ms * 1e3 / 20, n / (ms * 1e-3 / 20) / 1e9, 3.0 * n / (ms * 1e-3 / 20) / 1e9);
+            fflush(stdout);
+        };
+        time_it("product", [&] { CK(ocmk::launch_copy(b0, c0, a0, n, nullptr, ticket, st, nullptr)); });
+        time_it("two_memcpy", [&] {
+            CK(cudaMemcpyAsync(b0, a0, n, cudaMemcpyDefault, st));
+            CK(cudaMemcpyAsync(c0, a0, n, cudaMemcpyDefault, st));
+        });
+        for (int ctas : {296, 592, 1184, 2368}) {
+            char nm[64];
+            snprintf(nm, sizeof nm, "u2_na_%d", ctas);
+            time_it(nm, [&] { dual_kernel<2, 0><<<ctas, 256, 0, st>>>(a0, b0, c0, n); });
+            snprintf(nm, sizeof nm, "u4_na_%d", ctas);
+            time_it(nm, [&] { dual_kernel<4, 0><<<ctas, 256, 0, st>>>(a0, b0, c0, n); });
+            snprintf(nm, sizeof nm, "u2_cs_%d", ctas);
+            time_it(nm, [&] { dual_kernel<2, 1><<<ctas, 256, 0, st>>>(a0, b0, c0, n); });
+            snprintf(nm, sizeof nm, "u1_plain_%d", ctas);
+            time_it(nm, [&] { dual_kernel<1, 2><<<ctas, 256, 0, st>>>(a0, b0, c0, n); });
+        }
+        return 0;
     }
     std::vector<Variant> vars = {
         {"memcpy", 0, 0, 0, 0, 0},
