@@ -207,6 +207,15 @@ __global__ void ocm_signal_kernel(uint64_t *signal) {
     red_release_sys_add(signal, 1ull);
 }
 
+// Completion of a LARGE copy: published by a one-thread kernel that follows the copy kernel on the stream.
+// The kernel boundary orders every byte; this avoids a release in each of the ~2400 CTAs of the copy
+// (measured 8-14 us on a 128 us two-destination copy; the extra launch costs ~1 us on the device).
+__global__ void ocm_complete_kernel(uint64_t *signal, uint64_t *done_flag, uint64_t done_value) {
+    asm volatile("fence.acq_rel.sys;" ::: "memory");
+    if (signal) red_release_sys_add(signal, 1ull);
+    if (done_flag) st_release_sys(done_flag, done_value);
+}
+
 // ------------------------------------------------------------------ host ----
 int num_sms(int device) {
     static int cached[64] = {0};
@@ -296,8 +305,16 @@ cudaError_t launch_copy(void *dst, void *dst2, const void *src, size_t bytes, ui
         int cap = t.ctas > 0 ? t.ctas : sms * (dst2 ? 16 : 4);
         int ctas = (int)std::min<uint64_t>(std::max<uint64_t>(want, 1), (uint64_t)cap);
         if (ctas > 1 && signal && !ticket) return cudaErrorInvalidValue;
+        // many CTAs: completion moves to a follow-up one-thread kernel (see ocm_complete_kernel)
+        const bool split = (a.signal || a.done_flag) && ctas > sms * 4;
+        uint64_t *sig = a.signal, *flag = a.done_flag;
+        if (split) a.signal = a.done_flag = nullptr;
         if (dst2) ocm_copy_v32_kernel<true><<<ctas, 256, 0, stream>>>(a);
         else ocm_copy_v32_kernel<false><<<ctas, 256, 0, stream>>>(a);
+        if (split) {
+            ocm_complete_kernel<<<1, 1, 0, stream>>>(sig, flag, a.done_value);
+            if (launches) ++*launches;
+        }
     } else if (bulk) {
         int agents = std::min(std::max(t.agents, 1), kMaxAgents);
         int stages = std::min(std::max(t.stages, 2), kMaxStages);
