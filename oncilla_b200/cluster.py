@@ -156,6 +156,7 @@ class LocalCluster:
         e["OCM_NS"] = self.ns
         e["OCM_RANK"] = str(rank)
         e["OCM_LOG"] = self.log_level
+        e["OCM_DIE_WITH_PARENT"] = "1"      # read by the daemons only: they exit when this harness dies
         return e
 
     def apply_env(self, rank: int = 0) -> None:

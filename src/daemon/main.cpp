@@ -3,8 +3,11 @@
 // src/main.c:162-166,187-224) with optional overrides.
 #include "daemon.hpp"
 #include "../common/log.hpp"
+#include <csignal>
 #include <cstdio>
 #include <cstring>
+#include <sys/prctl.h>
+#include <unistd.h>
 
 static void usage(const char *argv0) {
     fprintf(stderr,
@@ -39,6 +42,11 @@ int main(int argc, char **argv) {
     if (o.nodefile.empty()) {
         usage(argv[0]);
         return 2;
+    }
+    // launched by a harness (LocalCluster): do not outlive it, so a killed benchmark cannot leak pools
+    if (getenv("OCM_DIE_WITH_PARENT")) {
+        prctl(PR_SET_PDEATHSIG, SIGTERM);
+        if (getppid() == 1) return 1;   // the parent is already gone
     }
     ocm::Daemon d(o);
     int r = d.init();
