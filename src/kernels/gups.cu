@@ -19,22 +19,23 @@ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
 }
 
 // word index in the logical table -> address in the owning rank's slab
-__device__ __forceinline__ uint64_t *gups_addr(const GupsTable &t, uint64_t idx) {
-    uint64_t stripe = idx / t.words_per_stripe;
-    uint64_t within = idx & (t.words_per_stripe - 1);
-    uint64_t rank = stripe % (uint64_t)t.n_ranks;
-    uint64_t local_stripe = stripe / (uint64_t)t.n_ranks;
-    return t.base[rank] + local_stripe * t.words_per_stripe + within;
+// (shifts and 32-bit division: a 64-bit divide per update would cost more than the update itself)
+__device__ __forceinline__ uint64_t *gups_addr(const GupsTable &t, uint64_t idx, unsigned shift) {
+    const uint32_t stripe = (uint32_t)(idx >> shift);
+    const uint64_t within = idx & (t.words_per_stripe - 1);
+    const uint32_t rank = stripe % (uint32_t)t.n_ranks;
+    const uint32_t local_stripe = stripe / (uint32_t)t.n_ranks;
+    return t.base[rank] + ((uint64_t)local_stripe << shift) + within;
 }
 
-__global__ void __launch_bounds__(256) ocm_gups_kernel(GupsTable t, uint64_t n_updates, uint64_t seed) {
+__global__ void __launch_bounds__(256) ocm_gups_kernel(GupsTable t, uint64_t n_updates, uint64_t seed, unsigned shift) {
     const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t mask = t.total_words - 1;
     uint64_t step = 0;
     // 4 independent updates in flight per thread
     for (uint64_t u = tid; u < n_updates; u += kGupsThreads, ++step) {
         uint64_t v = mix64(seed + tid * 0x9E3779B97F4A7C15ull + step * 0xD1B54A32D192ED03ull);
-        uint64_t *p = gups_addr(t, v & mask);
+        uint64_t *p = gups_addr(t, v & mask, shift);
         asm volatile("red.global.xor.b64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
     }
 }
@@ -55,7 +56,9 @@ cudaError_t launch_gups(const GupsTable &t, uint64_t n_updates, uint64_t seed, c
     if (t.n_ranks < 1 || t.n_ranks > 64 || (t.total_words & (t.total_words - 1)) ||
         (t.words_per_stripe & (t.words_per_stripe - 1)) || t.words_per_stripe > t.total_words)
         return cudaErrorInvalidValue;
-    ocm_gups_kernel<<<(unsigned)(kGupsThreads / 256), 256, 0, stream>>>(t, n_updates, seed);
+    if (t.total_words / t.words_per_stripe > 0xFFFFFFFFull) return cudaErrorInvalidValue;
+    const unsigned shift = (unsigned)__builtin_ctzll(t.words_per_stripe);
+    ocm_gups_kernel<<<(unsigned)(kGupsThreads / 256), 256, 0, stream>>>(t, n_updates, seed, shift);
     return cudaGetLastError();
 }
 

@@ -27,11 +27,28 @@ struct RowMap {
     int64_t  ds0, ds1, ds2;       // destination strides (bytes)
 };
 
+// 64-bit integer division is ~100 instructions on the SM: take the 32-bit path whenever the operands fit
+// (the cast kernel was issue-bound on its index arithmetic, profiles/README.md §5).
+__device__ __forceinline__ void divmod(uint64_t a, uint64_t b, uint64_t *q, uint64_t *r) {
+    if (((a | b) >> 32) == 0) {
+        const uint32_t a32 = (uint32_t)a, b32 = (uint32_t)b;
+        *q = a32 / b32;
+        *r = a32 % b32;
+    } else {
+        *q = a / b;
+        *r = a % b;
+    }
+}
+
 __device__ __forceinline__ void row_offsets(const RowMap &m, uint64_t row, int64_t *so, int64_t *dof) {
-    uint64_t i1 = row % m.n0;
-    uint64_t t = row / m.n0;
-    uint64_t i2 = t % m.n1;
-    uint64_t i3 = t / m.n1;
+    if (m.n1 == 1 && m.n2 == 1) {   // plain 2-D case: no division at all
+        *so = (int64_t)row * m.ss0;
+        *dof = (int64_t)row * m.ds0;
+        return;
+    }
+    uint64_t i1, t, i2, i3;
+    divmod(row, m.n0, &t, &i1);
+    divmod(t, m.n1, &i3, &i2);
     *so = (int64_t)i1 * m.ss0 + (int64_t)i2 * m.ss1 + (int64_t)i3 * m.ss2;
     *dof = (int64_t)i1 * m.ds0 + (int64_t)i2 * m.ds1 + (int64_t)i3 * m.ds2;
 }
@@ -139,7 +156,8 @@ __global__ void __launch_bounds__(256) ocm_strided_vec_kernel(StridedArgs a) {
     const uint64_t total = a.rows * vpr;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-        uint64_t row = i / vpr, v = i % vpr;
+        uint64_t row, v;
+        divmod(i, vpr, &row, &v);
         int64_t so, dof;
         row_offsets(a.map, row, &so, &dof);
         *reinterpret_cast<VT *>(a.dst + dof + (int64_t)(v * V)) =
@@ -217,7 +235,8 @@ __device__ __forceinline__ void store8(uint8_t *p, int dt, const float v[8]) {
 __global__ void __launch_bounds__(256) ocm_cast_kernel(CastArgs a) {
     const bool quant = a.dst_dtype == DT_F8E4M3 && a.src_dtype != DT_F8E4M3;
     const bool dequant = a.src_dtype == DT_F8E4M3 && a.dst_dtype != DT_F8E4M3;
-    const uint32_t G = a.blk ? a.blk / 8 : 1;
+    const uint32_t G = a.blk ? a.blk / 8 : 1;                 // 1, 4 or 16: always a power of two
+    const uint32_t gshift = G == 16 ? 4 : G == 4 ? 2 : 0;
     const uint64_t cpr = a.blk ? (uint64_t)a.bpr * G : (a.elems + 7) / 8;   // chunks per row, padded to whole blocks
     const uint64_t total = a.rows * cpr;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -225,7 +244,8 @@ __global__ void __launch_bounds__(256) ocm_cast_kernel(CastArgs a) {
     // all lanes of a warp iterate together (shuffles below)
     const uint64_t total_pad = (total + 31) & ~31ull;
     for (uint64_t c = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; c < total_pad; c += stride) {
-        const uint64_t row = c / cpr, ch = c % cpr;
+        uint64_t row, ch;
+        divmod(c, cpr, &row, &ch);
         const uint64_t e0 = ch * 8;
         const bool valid = c < total && e0 < a.elems;
         float v[8];
@@ -247,12 +267,12 @@ __global__ void __launch_bounds__(256) ocm_cast_kernel(CastArgs a) {
             const float scale = amax > 1e-30f ? __fdiv_rn(amax, 448.0f) : 1.0f;   // (near-)zero block: scale 1
             const float inv = __fdiv_rn(1.0f, scale);
             if (valid) {
-                if ((ch % G) == 0) a.scales[row * a.bpr + ch / G] = scale;
+                if ((ch & (G - 1)) == 0) a.scales[row * a.bpr + (ch >> gshift)] = scale;
 #pragma unroll
                 for (int i = 0; i < 8; ++i) v[i] = __fmul_rn(v[i], inv);
             }
         } else if (dequant && valid) {
-            const float scale = a.scales[row * a.bpr + ch / G];
+            const float scale = a.scales[row * a.bpr + (ch >> gshift)];
 #pragma unroll
             for (int i = 0; i < 8; ++i) v[i] = __fmul_rn(v[i], scale);
         }
@@ -287,7 +307,8 @@ __global__ void __launch_bounds__(256) ocm_cast_scalar_kernel(CastArgs a) {
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     const size_t ss = dtype_size(a.src_dtype), ds = dtype_size(a.dst_dtype);
     for (uint64_t c = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; c < total; c += stride) {
-        const uint64_t row = c / spr, b = c % spr;
+        uint64_t row, b;
+        divmod(c, spr, &row, &b);
         const uint64_t lo = b * span, hi = lo + span < a.elems ? lo + span : a.elems;
         int64_t so, dof;
         row_offsets(a.map, row, &so, &dof);
