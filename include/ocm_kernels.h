@@ -67,7 +67,7 @@ int ocmk_sort_u64(uint64_t *keys, uint64_t *tmp, uint64_t n, void *stream);
 /* Same sort for callers that must not allocate device memory: applications whose cluster daemons
  * have claimed nearly all HBM for their pools (a cudaMalloc for scratch could fail), and callers
  * inside latency-critical sections where cudaMalloc/cudaFree could stall the device.  The scratch is
- * a fixed 384 KiB array inside the library, shared by every call on a GPU: at most
+ * a fixed 388 KiB array inside the library, shared by every call on a GPU: at most
  * OCMK_SORT_NOALLOC_MAX_KEYS keys per call (more is refused with -OCM_ERANGE), calls that overlap on
  * one GPU race on the scratch, and the first call on a device (which looks up the array's device
  * address) should happen before any stream capture begins.  It has no counterpart in the reference. */
