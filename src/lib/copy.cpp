@@ -194,11 +194,14 @@ static int single_copy(const Side &dst, uint64_t dst_off, const Side &src, uint6
                     "cudaMemcpyAsync");
 }
 
+// [off, off+n) lies inside the side (written so that huge offsets cannot wrap around)
+static inline bool fits(const Side &s, uint64_t off, uint64_t n) { return n <= s.bytes && off <= s.bytes - n; }
+
 int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2_off, const Side &src, uint64_t src_off,
               uint64_t bytes, Region *signal_rec, void *stream, bool *used_stream) {
     Ctx &c = ctx();
     if (!dst.ptr || !src.ptr || (dst2 && !dst2->ptr)) return OCM_EINVAL;
-    if (src_off + bytes > src.bytes || dst_off + bytes > dst.bytes || (dst2 && dst2_off + bytes > dst2->bytes))
+    if (!fits(src, src_off, bytes) || !fits(dst, dst_off, bytes) || (dst2 && !fits(*dst2, dst2_off, bytes)))
         return OCM_ERANGE;
     c.n_copies.fetch_add(1, std::memory_order_relaxed);
     c.copy_bytes.fetch_add(bytes, std::memory_order_relaxed);
@@ -364,6 +367,8 @@ static int do_copy(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p,
         } else if (p->src_offset_2 == p->dest_offset) {
             err = side_copy(*dfar, p->dest_offset_2, &dst->local, p->dest_offset, src->local, p->src_offset, n,
                             dfar->rec, stream, used);
+        } else if (!fits(dst->local, p->src_offset_2, n) || !fits(*dfar, p->dest_offset_2, n)) {
+            err = OCM_ERANGE;   // checked up front so that a bad second hop does not leave the first one done
         } else {
             err = side_copy(dst->local, p->dest_offset, nullptr, 0, src->local, p->src_offset, n, nullptr, stream, used);
             if (!err)
@@ -376,6 +381,8 @@ static int do_copy(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p,
         } else if (p->src_offset_2 == p->src_offset) {
             err = side_copy(dst->local, p->dest_offset_2, &src->local, p->src_offset, *sfar, p->dest_offset, n,
                             dst->local.rec, stream, used);
+        } else if (!fits(src->local, p->src_offset_2, n) || !fits(dst->local, p->dest_offset_2, n)) {
+            err = OCM_ERANGE;
         } else {
             err = side_copy(src->local, p->src_offset, nullptr, 0, *sfar, p->dest_offset, n, nullptr, stream, used);
             if (!err)

@@ -109,6 +109,83 @@ def test_python_api_host_kinds(cluster2, path):
     assert res["double_free_noop"]
 
 
+COPY_MODEL_SNIPPET = r"""
+import json, random, torch
+import oncilla_b200 as ocm
+ocm.init()
+rng = random.Random(1234)
+L, R = 6000, 9000                                  # window / far-side sizes of the pairs
+loc = [ocm.alloc(ocm.OCM_LOCAL_HOST, 7000) for _ in range(2)]
+pair = [ocm.alloc(ocm.OCM_REMOTE_HOST, L, R) for _ in range(2)]
+# python model of every side
+m_loc = [bytearray(7000) for _ in range(2)]
+m_win = [bytearray(L) for _ in range(2)]
+m_far = [bytearray(R) for _ in range(2)]
+def fill(t, model):
+    data = bytes(rng.randrange(256) for _ in range(len(model)))
+    model[:] = data
+    t[:] = torch.frombuffer(bytearray(data), dtype=torch.uint8)
+for i in range(2):
+    fill(loc[i].local_tensor(), m_loc[i]); fill(pair[i].local_tensor(), m_win[i]); fill(pair[i].remote_tensor(), m_far[i])
+bad = 0; ops = 0; rejected = 0
+for it in range(400):
+    n = rng.randrange(1, 3000)
+    so, do, so2, do2 = (rng.randrange(0, 5500) for _ in range(4))
+    if rng.random() < 0.5: so2 = rng.choice([so, do])   # second hop starts where the first landed -> fused path
+    kind = rng.choice(["l2l", "l2p", "p2l", "p2p", "put", "get"])
+    a, b = rng.randrange(2), rng.randrange(2)
+    flag = rng.choice([0, 1])
+    try:
+        if kind in ("put", "get"):
+            op = 1 if kind == "put" else 0
+            ok = n <= L and so + n <= L and do + n <= R
+            (pair[a].put if op else pair[a].get)(n, src_offset=so, dest_offset=do)
+            if not ok: bad += 1; continue
+            if op: m_far[a][do:do+n] = m_win[a][so:so+n]
+            else: m_win[a][so:so+n] = m_far[a][do:do+n]
+        else:
+            dst, src = {"l2l": (loc[a], loc[1-a]), "l2p": (pair[a], loc[b]), "p2l": (loc[a], pair[b]), "p2p": (pair[a], pair[1-a])}[kind]
+            # what the call means once op_flag=0 has swapped the roles
+            eff = kind if flag else {"l2l": "l2l", "l2p": "p2l", "p2l": "l2p", "p2p": "p2p"}[kind]
+            D, S = (a, 1-a) if kind == "l2l" else (a, b) if kind in ("l2p", "p2l") else (a, 1-a)
+            if not flag: D, S = S, D
+            if eff == "l2l": ok = so + n <= 7000 and do + n <= 7000
+            elif eff == "l2p":
+                ok = so + n <= 7000 and do + n <= L and so2 + n <= L and do2 + n <= R
+            elif eff == "p2l":
+                ok = do + n <= R and so + n <= L and so2 + n <= L and do2 + n <= 7000
+            else: ok = so + n <= R and do + n <= R
+            ocm.copy(dst, src, n, src_offset=so, dest_offset=do, src_offset_2=so2, dest_offset_2=do2, op_flag=flag)
+            if not ok: bad += 1; continue
+            if eff == "l2l": m_loc[D][do:do+n] = m_loc[S][so:so+n]
+            elif eff == "l2p":
+                m_win[D][do:do+n] = m_loc[S][so:so+n]; m_far[D][do2:do2+n] = m_win[D][so2:so2+n]
+            elif eff == "p2l":
+                m_win[S][so:so+n] = m_far[S][do:do+n]; m_loc[D][do2:do2+n] = m_win[S][so2:so2+n]
+            else: m_far[D][do:do+n] = m_far[S][so:so+n]
+        ops += 1
+    except ocm.OcmError as e:
+        rejected += 1
+        if ok: bad += 1                               # a valid request must not be rejected
+def same(t, model): return bytes(t.numpy().tobytes()) == bytes(model)
+for i in range(2):
+    if not (same(loc[i].local_tensor(), m_loc[i]) and same(pair[i].local_tensor(), m_win[i]) and same(pair[i].remote_tensor(), m_far[i])):
+        bad += 1000
+for x in loc + pair: x.free()
+ocm.tini()
+print("RESULT " + json.dumps({"bad": bad, "ops": ops, "rejected": rejected}))
+"""
+
+
+def test_copy_semantics_against_model(cluster2):
+    """400 random ocm_copy / put / get calls (all offset fields, both op_flags, fused and split hops, out-of-range
+    requests) on host kinds, checked byte for byte against a Python model of DESIGN.md section 4."""
+    out = _ok(run_py(cluster2, 0, COPY_MODEL_SNIPPET))
+    res = json.loads(out.split("RESULT ", 1)[1])
+    assert res["bad"] == 0, res
+    assert res["ops"] > 100 and res["rejected"] > 20
+
+
 def test_three_ranks_slow_path_forwarding():
     """REQ_ALLOC from rank 1 -> placement on rank 0 -> DO_ALLOC on rank 2 -> RELEASE_APP."""
     with ocm.LocalCluster(3, host_bytes=16 << 20, extra_env={"OCM_NO_GPU": "1"}) as cl:
