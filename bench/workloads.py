@@ -49,33 +49,50 @@ def main():
     ap.add_argument("--sort-keys", type=int, default=1 << 26)       # 512 MiB of keys per rank
     ap.add_argument("--sort-chunk", type=int, default=1 << 23)
     ap.add_argument("--hbm-frac", type=float, default=0.5, help="fraction of the sort's data allowed in peer HBM; rest spills to host")
+    ap.add_argument("--dsort-keys", type=int, default=1 << 24)      # 128 MiB of keys per rank, one global order
+    ap.add_argument("--only", choices=["dsort"], default=None, help="run just this section")
     args = ap.parse_args()
     tc = TorchrunCluster(gpu_bytes=8 << 30, host_bytes=3 << 30)
     with tc as (rank, world):
         # ---- config 3 ------------------------------------------------------------------------
         tc.barrier()
-        g = gups.run(total_words=args.gups_words, n_updates=args.gups_updates, iters=3)
-        tc.barrier()
-        worst = allmax(g["seconds"], world)
-        ok = allsum(1.0 if g["verified"] else 0.0, world) == world
-        if rank == 0:
+        if not args.only:
+            g = gups.run(total_words=args.gups_words, n_updates=args.gups_updates, iters=3)
+            tc.barrier()
+            worst = allmax(g["seconds"], world)
+            ok = allsum(1.0 if g["verified"] else 0.0, world) == world
+        if rank == 0 and not args.only:
             print(json.dumps({"kind": "gups", "n_gpus": world, "table_words_per_rank": args.gups_words,
                               "updates_per_rank": args.gups_updates, "seconds_max": round(worst, 6),
                               "GUPS_aggregate": round(world * args.gups_updates / worst / 1e9, 3), "verified": ok}), flush=True)
         # ---- config 4 ------------------------------------------------------------------------
         tc.barrier()
         # half of the runs (and of the output) fit the HBM budget, the rest spills to the pinned host tier
-        s = sort.run(total_keys=args.sort_keys, chunk_keys=args.sort_chunk,
-                     gpu_budget_total=int(args.hbm_frac * args.sort_keys * 8))
-        tc.barrier()
-        worst = allmax(s["seconds"], world)
-        ok = allsum(1.0 if s["ok"] else 0.0, world) == world
-        if rank == 0:
+        if not args.only:
+            s = sort.run(total_keys=args.sort_keys, chunk_keys=args.sort_chunk,
+                         gpu_budget_total=int(args.hbm_frac * args.sort_keys * 8))
+            tc.barrier()
+            worst = allmax(s["seconds"], world)
+            ok = allsum(1.0 if s["ok"] else 0.0, world) == world
+        if rank == 0 and not args.only:
             print(json.dumps({"kind": "ooc_sort", "n_gpus": world, "keys_per_rank": args.sort_keys,
                               "bytes_per_rank": args.sort_keys * 8, "seconds_max": round(worst, 4),
                               "Mkeys_per_s_aggregate": round(world * args.sort_keys / worst / 1e6, 1),
                               "bytes_in_hbm_rank0": s["bytes_in_hbm"], "bytes_in_host_rank0": s["bytes_in_host"],
                               "verified": ok}), flush=True)
+        # ---- distributed sample sort: all ranks sort one data set, keys exchanged by one-sided puts into
+        # shared blocks (ocm_share / ocm_attach) with completion signals ------------------------------------
+        from oncilla_b200.models import dsort
+
+        for it in range(2):                                   # first pass warms allocations and NCCL
+            d = dsort.run(keys_per_rank=args.dsort_keys)
+        if rank == 0:
+            print(json.dumps({"kind": "distributed_sort", "n_gpus": world, "keys_per_rank": args.dsort_keys,
+                              "seconds_max": round(d["seconds"], 5), "local_sort_s": round(d["local_sort_s"], 5),
+                              "exchange_s": round(d["exchange_s"], 5), "final_sort_s": round(d["final_sort_s"], 5),
+                              "Mkeys_per_s_aggregate": round(d["mkeys_per_s"], 1), "verified": d["ok"]}), flush=True)
+        if args.only == "dsort":
+            return
         # ---- config 5 (copy part): strided fp32 -> block-scaled fp8 put into the neighbour's HBM ----------
         rows, elems, pitch = 16384, 4096, 8192
         src = ocm.alloc(ocm.OCM_LOCAL_GPU, rows * pitch * 4)

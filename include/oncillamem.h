@@ -158,6 +158,32 @@ int ocm_quiet(void);
 int ocm_signal_read(ocm_alloc_t a, uint64_t *value);
 int ocm_signal_wait(ocm_alloc_t a, uint64_t at_least, int timeout_ms);
 
+/* ---- sharing an allocation between applications --------------------- */
+/* In the reference an allocation is private to the process that made it; the owner of the memory only
+ * learns about arriving data through the EXTOLL completer notification (reference src/extoll.c:145-170,
+ * src/extoll_server.c).  Here any application of the cluster can open a block that lives in a daemon's
+ * pool: the owner calls ocm_share() and hands the 32-byte token to its peers by any means (file, pipe,
+ * torch.distributed); a peer calls ocm_attach() and gets a window-less pair whose far side IS that
+ * block (ocm_remote_ptr, ocm_copy, ocm_copy_strided and the completion signal all work on it).  The
+ * signal word is shared too: the owner's ocm_signal_wait() returns once the peers' puts have landed.
+ * ocm_free() of an attached handle only drops the handle.  The block belongs to the owner: copies
+ * through an attached handle fail with OCM_ESTALE once the owner has freed it, and an owner that frees
+ * while peers still write is a use-after-free of the peers' making (as with CUDA IPC handles). */
+struct ocm_share_token {
+    uint64_t id;          /* allocation id on the rank that holds the block */
+    uint64_t bytes;
+    int32_t  rank;
+    uint32_t region;
+    uint32_t generation;
+    uint32_t tier;        /* 0 pinned host, 1 HBM */
+};
+/* The far side of a pair or the memory of a local kind; -OCM_EUNSUPPORTED for multi-slab kinds and for
+ * local kinds that fell back to malloc / cudaMalloc (src/lib.c:226,240 behaviour). */
+int ocm_share(ocm_alloc_t a, struct ocm_share_token *out);
+int ocm_attach(const struct ocm_share_token *tok, ocm_alloc_t *out);
+/* handles other applications currently hold on the block behind `a` (owner or attached handle) */
+int ocm_attach_count(ocm_alloc_t a);
+
 /* ---- strided / cast copies (kernels K4/K5) -------------------------- */
 enum ocm_dtype { OCM_U8 = 0, OCM_F32 = 1, OCM_BF16 = 2, OCM_F8E4M3 = 3 };
 

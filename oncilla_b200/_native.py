@@ -94,6 +94,11 @@ class ocm_strided(C.Structure):
                 ("scale_offset", C.c_uint64)]
 
 
+class ocm_share_token(C.Structure):
+    _fields_ = [("id", C.c_uint64), ("bytes", C.c_uint64), ("rank", C.c_int32), ("region", C.c_uint32),
+                ("generation", C.c_uint32), ("tier", C.c_uint32)]
+
+
 class ocm_stats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "allocs_live", "allocs_total", "frees_total", "bytes_gpu_live", "bytes_host_live", "copies", "copy_bytes",
@@ -145,6 +150,9 @@ _sig("ocm_copy_onesided_async", C.c_int, ocm_alloc_t, P(ocm_params), C.c_void_p)
 _sig("ocm_quiet", C.c_int)
 _sig("ocm_signal_read", C.c_int, ocm_alloc_t, P(C.c_uint64))
 _sig("ocm_signal_wait", C.c_int, ocm_alloc_t, C.c_uint64, C.c_int)
+_sig("ocm_share", C.c_int, ocm_alloc_t, P(ocm_share_token))
+_sig("ocm_attach", C.c_int, P(ocm_share_token), P(ocm_alloc_t))
+_sig("ocm_attach_count", C.c_int, ocm_alloc_t)
 _sig("ocm_copy_strided", C.c_int, ocm_alloc_t, ocm_alloc_t, P(ocm_strided), C.c_void_p)
 _sig("ocm_copy_onesided_strided", C.c_int, ocm_alloc_t, P(ocm_strided), C.c_void_p)
 _sig("ocm_get_stats", C.c_int, P(ocm_stats))

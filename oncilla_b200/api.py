@@ -210,6 +210,19 @@ class Allocation:
         if r:
             raise OcmError("ocm_signal_wait", r)
 
+    # ---- sharing between applications ---------------------------------------------------------
+    def share(self) -> bytes:
+        """A 32-byte token another application of the cluster passes to :func:`attach`."""
+        tok = N.ocm_share_token()
+        r = lib.ocm_share(self.handle, C.byref(tok))
+        if r:
+            raise OcmError("ocm_share", r)
+        return bytes(tok)
+
+    @property
+    def attach_count(self) -> int:
+        return lib.ocm_attach_count(self.handle)
+
     # ---- copies -----------------------------------------------------------------------------
     def put(self, nbytes: int | None = None, *, src_offset: int = 0, dest_offset: int = 0, stream="sync") -> None:
         """One-sided write window[src_offset] -> far side[dest_offset]."""
@@ -248,6 +261,20 @@ class Allocation:
 
 def alloc(kind: int, local_bytes: int = 0, remote_bytes: int = 0, **kw) -> Allocation:
     return Allocation(kind, local_bytes, remote_bytes, **kw)
+
+
+def attach(token: bytes) -> Allocation:
+    """Open a block another application shared (``Allocation.share()``): a window-less pair whose far side
+    is that block.  ``free()`` on it only drops the handle."""
+    tok = N.ocm_share_token.from_buffer_copy(token)
+    h = C.c_void_p(0)
+    r = lib.ocm_attach(C.byref(tok), C.byref(h))
+    if r or not h.value:
+        raise OcmError("ocm_attach", r)
+    a = Allocation.__new__(Allocation)
+    a._h = h.value
+    a.requested_kind = lib.ocm_alloc_kind(a._h)
+    return a
 
 
 def _onesided(a: Allocation, op: int, nbytes, src_offset, dest_offset, stream) -> None:

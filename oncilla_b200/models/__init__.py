@@ -6,5 +6,7 @@ allocations and our kernels:
 
 * ``gups``  - pooled-HBM random access over a striped allocation (config 3)
 * ``sort``  - out-of-core sort of synthetic keys over peer HBM + pinned host (config 4)
+* ``dsort`` - distributed sample sort: every rank sorts, keys are exchanged with one-sided puts into
+              blocks shared between the applications (``ocm_share`` / ``ocm_attach``) and per-block signals
 """
-from . import gups, sort  # noqa: F401
+from . import dsort, gups, sort  # noqa: F401

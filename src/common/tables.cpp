@@ -263,6 +263,7 @@ int pool_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int rank, Bloc
     r.id = h->next_id.fetch_add(1, std::memory_order_relaxed);
     r.generation += 1;
     r.flags = 0;
+    r.attached.store(0, std::memory_order_relaxed);
     r.signal.store(0, std::memory_order_relaxed);
     r.state.store(REGION_LIVE, std::memory_order_release);
     p.used_bytes.fetch_add(block_bytes, std::memory_order_relaxed);

@@ -33,7 +33,7 @@
 namespace ocm {
 
 constexpr uint64_t kTableMagic   = 0x4F434D5441424C45ull; // "OCMTABLE"
-constexpr uint32_t kTableVersion = 4;
+constexpr uint32_t kTableVersion = 5;
 constexpr uint32_t kMaxGranules  = 1u << 18;
 constexpr uint64_t kMcGranule     = 64ull << 10;
 constexpr uint32_t kMcMaxGranules = 1u << 14;     // multicast region <= 1 GiB
@@ -52,7 +52,8 @@ struct alignas(64) Region {
     uint64_t              id;          // rem_alloc_id
     std::atomic<uint64_t> signal;      // completion counter (puts add 1)
     uint64_t              flags;
-    uint64_t              reserved;
+    std::atomic<uint32_t> attached;    // handles other applications hold on this block (ocm_attach)
+    uint32_t              reserved;
 };
 static_assert(sizeof(Region) == 64, "one cache line per region");
 

@@ -210,6 +210,12 @@ static void *side_ptr(RankView *v, int tier, uint64_t offset) {
 
 static int release_side(Side &s);
 
+// Drop one ocm_attach reference; never below zero (the count restarts at 0 when a block is recycled).
+static void attached_dec(Region *rec) {
+    uint32_t v = rec->attached.load(std::memory_order_relaxed);
+    while (v && !rec->attached.compare_exchange_weak(v, v - 1, std::memory_order_acq_rel)) {}
+}
+
 // Allocate one side through the shared tables (fast) or the daemon (slow).
 static int alloc_side(uint32_t type, uint64_t bytes, int policy, int explicit_rank, uint32_t flags, Side *out) {
     Ctx &c = ctx();
@@ -313,6 +319,12 @@ static int release_side(Side &s) {
         c.bytes_live[TIER_GPU].fetch_sub(s.bytes, std::memory_order_relaxed);
         break;
     }
+    case SIDE_ATTACHED:
+        // someone else's block: only the attach count goes down (unless the block has been recycled since)
+        if (s.rec && s.rec->id == s.id && s.rec->generation == s.generation &&
+            s.rec->state.load(std::memory_order_acquire) == REGION_LIVE)
+            attached_dec(s.rec);
+        break;
     default: break;
     }
     s = Side();
@@ -787,6 +799,85 @@ int ocm_signal_wait(ocm_alloc_t a, uint64_t at_least, int timeout_ms) {
         if (timeout_ms >= 0 && mono_ns() > deadline) return -OCM_ESTALE;
         if (spin > 1000) usleep(20);
     }
+}
+
+// ------------------------------------------------ sharing between applications --
+// The side of `a` another application may open: the far side of a pair, else the local memory.
+static const Side *shareable_side(ocm_alloc_t a) {
+    if (!a->stripes.empty() || a->mc) return nullptr;
+    const Side &s = (a->paired && a->remote.valid()) ? a->remote : a->local;
+    return (s.backing == SIDE_POOL || s.backing == SIDE_ATTACHED) && s.rec ? &s : nullptr;
+}
+
+int ocm_share(ocm_alloc_t a, struct ocm_share_token *out) {
+    if (!valid_handle(a) || !out) return -OCM_EINVAL;
+    const Side *s = shareable_side(a);
+    if (!s) return -OCM_EUNSUPPORTED;
+    memset(out, 0, sizeof *out);
+    out->id = s->id;
+    out->bytes = s->bytes;
+    out->rank = s->rank;
+    out->region = s->region;
+    out->generation = s->generation;
+    out->tier = s->tier;
+    return 0;
+}
+
+int ocm_attach(const struct ocm_share_token *tok, ocm_alloc_t *out) {
+    TraceRange tr_("ocm_attach");
+    Ctx &c = ctx();
+    if (!tok || !out) return -OCM_EINVAL;
+    *out = nullptr;
+    if (!c.inited || !c.cluster) return -OCM_ENODAEMON;
+    if (tok->rank < 0 || tok->rank >= c.n_ranks || tok->tier >= (uint32_t)TIER_COUNT) return -OCM_EINVAL;
+    if (tok->tier == TIER_GPU && c.device < 0) return -OCM_ENOGPU;
+    RankView *v = get_view(tok->rank, tok->tier == TIER_GPU);
+    if (!v) return -OCM_ENODAEMON;
+    const PoolDesc &pd = v->hdr->pool[tok->tier];
+    if (tok->region >= pd.n_granules) return -OCM_EINVAL;
+    Region *rec = &table_regions(v->hdr, (int)tok->tier)[tok->region];
+    // count ourselves in first, then check that the block is (still) the one the token names
+    rec->attached.fetch_add(1, std::memory_order_acq_rel);
+    const bool live = rec->state.load(std::memory_order_acquire) == REGION_LIVE && rec->id == tok->id &&
+                      rec->generation == tok->generation && rec->bytes == tok->bytes;
+    void *ptr = live ? side_ptr(v, (int)tok->tier, (uint64_t)tok->region * pd.granule) : nullptr;
+    if (!ptr) {
+        attached_dec(rec);
+        return live ? (tok->tier == TIER_GPU ? -OCM_ENOGPU : -OCM_ENODAEMON) : -OCM_ESTALE;
+    }
+    lib_alloc *a = new lib_alloc();
+    a->magic = kAllocMagic;
+    a->kind = tok->tier == TIER_GPU ? OCM_REMOTE_GPU : OCM_REMOTE_HOST;
+    a->paired = true;
+    a->stripe_bytes = 0;
+    a->mc = false;
+    a->mc_offset = 0;
+    a->mc_ptr = nullptr;
+    a->lib_stream_pending.store(false);
+    Side &s = a->remote;
+    s.backing = SIDE_ATTACHED;
+    s.tier = (uint8_t)tok->tier;
+    s.rank = tok->rank;
+    s.region = tok->region;
+    s.generation = tok->generation;
+    s.id = tok->id;
+    s.offset = (uint64_t)tok->region * pd.granule;
+    s.bytes = tok->bytes;
+    s.ptr = ptr;
+    s.rec = rec;
+    {
+        std::lock_guard<std::mutex> g(c.mu);
+        c.allocs.insert(a);
+    }
+    c.n_alloc.fetch_add(1, std::memory_order_relaxed);
+    *out = a;
+    return 0;
+}
+
+int ocm_attach_count(ocm_alloc_t a) {
+    if (!valid_handle(a)) return -OCM_EINVAL;
+    const Side *s = shareable_side(a);
+    return s ? (int)s->rec->attached.load(std::memory_order_acquire) : -OCM_EUNSUPPORTED;
 }
 
 int ocm_get_stats(struct ocm_stats *out) {

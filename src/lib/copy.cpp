@@ -263,6 +263,8 @@ int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2
 
 static bool valid(ocm_alloc_t a) { return a && a->magic == kAllocMagic; }
 
+static bool stale(ocm_alloc_t a) { return side_stale(a->remote); }
+
 // The far side of a pair (single slab kinds only).
 static const Side *far_side(ocm_alloc_t a) { return (a->paired && a->remote.valid()) ? &a->remote : nullptr; }
 
@@ -340,6 +342,7 @@ static int stripes_xfer(ocm_alloc_t a, bool to_far, const Side &local, uint64_t 
 
 static int do_copy(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p, void *stream, bool *used) {
     if (!valid(dst) || !valid(src) || !p) return OCM_EINVAL;
+    if (stale(dst) || stale(src)) return OCM_ESTALE;
     if (!p->op_flag) std::swap(dst, src);   // "read": data flows the other way (src/lib.c:510-515)
     if (!dst->stripes.empty() && !src->stripes.empty()) return OCM_EUNSUPPORTED;
     if (!dst->stripes.empty() || !src->stripes.empty()) {

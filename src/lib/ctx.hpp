@@ -40,7 +40,8 @@ struct PeerExec {
 };
 
 enum SideBacking : uint8_t { SIDE_NONE = 0, SIDE_POOL = 1, SIDE_HEAP = 2, SIDE_CUDAMALLOC = 3, SIDE_USER = 4,
-                             SIDE_MC = 5 /* replica inside the NVLS multicast region */ };
+                             SIDE_MC = 5 /* replica inside the NVLS multicast region */,
+                             SIDE_ATTACHED = 6 /* another application's pool block (ocm_attach); never released here */ };
 
 // One contiguous piece of memory addressable from this process.
 struct Side {
@@ -57,6 +58,13 @@ struct Side {
     Region     *rec = nullptr;        // table record (signal word lives here)
     bool valid() const { return backing != SIDE_NONE; }
 };
+
+// An attached side (ocm_attach) goes stale when the owner frees the block.
+inline bool side_stale(const Side &s) {
+    return s.backing == SIDE_ATTACHED &&
+           !(s.rec->state.load(std::memory_order_acquire) == REGION_LIVE && s.rec->id == s.id &&
+             s.rec->generation == s.generation);
+}
 
 } // namespace ocm
 

@@ -219,6 +219,7 @@ static int strided_sides(const Side &dst, const Side &src, const struct ocm_stri
 int ocm_copy_strided(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_strided *d, void *stream) {
     if (!dst || !src || !d || dst->magic != kAllocMagic || src->magic != kAllocMagic) return -OCM_EINVAL;
     if (!dst->stripes.empty() || !src->stripes.empty()) return -OCM_EUNSUPPORTED;
+    if (side_stale(dst->remote) || side_stale(src->remote)) return -OCM_ESTALE;
     if (!d->op_flag) std::swap(dst, src);
     // the far side is the target when there is one, like a one-hop ocm_copy
     const Side &D = (dst->paired && dst->remote.valid()) ? dst->remote : dst->local;

@@ -59,10 +59,10 @@ def run_app(cl, rank, argv, timeout=120, env_extra=None):
     return subprocess.run([str(a) for a in argv], env=env, capture_output=True, text=True, timeout=timeout)
 
 
-def run_py(cl, rank, code, timeout=180, env_extra=None):
+def run_py(cl, rank, code, timeout=180, env_extra=None, argv=()):
     """Run a Python snippet in a fresh process attached to ``rank``'s daemon."""
     env = cl.env(rank)
     env["PYTHONPATH"] = str(REPO) + os.pathsep + env.get("PYTHONPATH", "")
     if env_extra:
         env.update(env_extra)
-    return subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=timeout)
+    return subprocess.run([sys.executable, "-c", code, *argv], env=env, capture_output=True, text=True, timeout=timeout)

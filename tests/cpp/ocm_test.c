@@ -235,12 +235,58 @@ static int bw_test(int sub, uint64_t max_b, int iters) {
     return 0;
 }
 
+/* Test 5: open an allocation a second time through a share token, write through the attached handle,
+ * watch the owner's signal, check the bounds and the stale-handle detection. */
+static int share_test(int sub, uint64_t size_b) {
+    struct ocm_alloc_params ap;
+    struct ocm_params cp;
+    struct ocm_share_token tok;
+    ocm_alloc_t owner, src, att = NULL, att2 = NULL;
+    uint64_t sig = 99;
+    size_t rsz = 0;
+    const int gpu = sub == 2 || sub == 7;
+    memset(&ap, 0, sizeof ap);
+    ap.kind = kind_of(sub);
+    ap.local_alloc_bytes = size_b;
+    ap.rem_alloc_bytes = size_b;
+    owner = ocm_alloc(&ap);
+    EXPECT(owner != NULL, "ocm_alloc owner: %s", ocm_strerror(ocm_last_error()));
+    ap.kind = gpu ? OCM_LOCAL_GPU : OCM_LOCAL_HOST;
+    src = ocm_alloc(&ap);
+    EXPECT(src != NULL, "ocm_alloc src");
+    if (!owner || !src) return -1;
+    EXPECT(ocm_share(owner, &tok) == 0, "ocm_share");
+    EXPECT(tok.bytes == size_b, "token bytes");
+    EXPECT(ocm_attach(&tok, &att) == 0 && att, "ocm_attach");
+    if (!att) return -1;
+    EXPECT(ocm_attach_count(owner) == 1, "attach count %d", ocm_attach_count(owner));
+    EXPECT(ocm_is_remote(att) && ocm_remote_sz(att, &rsz) == 0 && rsz == size_b, "attached handle is a pair of %zu", rsz);
+    EXPECT(ocm_remote_rank(att) == tok.rank, "owner rank");
+    memset(&cp, 0, sizeof cp);
+    cp.op_flag = 1;
+    cp.bytes = size_b;
+    EXPECT(ocm_copy(att, src, &cp) == 0, "copy through the attached handle: %s", ocm_strerror(ocm_last_error()));
+    EXPECT(ocm_signal_read(owner, &sig) == 0 && sig == 1, "owner signal %llu", (unsigned long long)sig);
+    cp.bytes = size_b + 1;
+    EXPECT(ocm_copy(att, src, &cp) != 0 && ocm_last_error() == OCM_ERANGE, "oversize copy must be rejected");
+    cp.bytes = size_b;
+    tok.generation += 1;
+    EXPECT(ocm_attach(&tok, &att2) == -OCM_ESTALE && !att2, "forged token must be rejected");
+    tok.generation -= 1;
+    EXPECT(ocm_free(owner) == 0, "owner free");
+    EXPECT(ocm_copy(att, src, &cp) != 0 && ocm_last_error() == OCM_ESTALE, "stale handle must be rejected");
+    EXPECT(ocm_attach(&tok, &att2) == -OCM_ESTALE, "attach after free must be rejected");
+    EXPECT(ocm_free(att) == 0, "free attached");
+    EXPECT(ocm_free(src) == 0, "free src");
+    return 0;
+}
+
 int main(int argc, char **argv) {
     int test, sub = 1, iters = 5;
     double mb1 = 1.0, mb2 = 1.0;
     uint64_t b1, b2;
     if (argc < 2) {
-        fprintf(stderr, "Usage: %s <1=alloc|2=onesided|3=twosided|4=bw> [alloc1 MB] [alloc2 MB] [kind] [iters]\n", argv[0]);
+        fprintf(stderr, "Usage: %s <1=alloc|2=onesided|3=twosided|4=bw|5=share> [alloc1 MB] [alloc2 MB] [kind] [iters]\n", argv[0]);
         return 2;
     }
     test = atoi(argv[1]);
@@ -260,6 +306,7 @@ int main(int argc, char **argv) {
     case 2: onesided_test(sub < 3 ? 3 : sub, b1); break;
     case 3: twosided_test(b1, b2, ocm_device() >= 0 && sub != 1); break;
     case 4: bw_test(sub < 3 ? 3 : sub, b1, iters); break;
+    case 5: share_test(sub, b1); break;
     default: printf("FAIL: unknown test\n"); g_fail++; break;
     }
     if (ocm_tini() != 0) {

@@ -24,7 +24,8 @@ def _ok(r):
 
 @pytest.mark.parametrize("path", ["fast", "daemon"])
 @pytest.mark.parametrize("test,args", [(1, ["1", "2", "1"]), (1, ["1", "2", "3"]), (1, ["1", "2", "8"]),
-                                       (2, ["1", "1", "3"]), (3, ["1", "1", "1"]), (4, ["0.25", "0.25", "3", "2"])])
+                                       (2, ["1", "1", "3"]), (3, ["1", "1", "1"]), (4, ["0.25", "0.25", "3", "2"]),
+                                       (5, ["1", "1", "1"]), (5, ["1", "1", "8"])])
 def test_ocm_test_program(cluster2, path, test, args):
     out = _ok(run_app(cluster2, 1, [BIN / "ocm_test", test, *args], env_extra={"OCM_ALLOC_PATH": path}))
     assert "pass: OCM test completed successfully" in out
@@ -184,6 +185,85 @@ def test_copy_semantics_against_model(cluster2):
     res = json.loads(out.split("RESULT ", 1)[1])
     assert res["bad"] == 0, res
     assert res["ops"] > 100 and res["rejected"] > 20
+
+
+SHARE_OWNER = r"""
+import json, os, time, torch
+import oncilla_b200 as ocm
+d = os.environ["SHARE_DIR"]
+ocm.init()
+a = ocm.alloc(ocm.OCM_LOCAL_HOST, 1 << 20)
+open(d + "/token.tmp", "wb").write(a.share()); os.rename(d + "/token.tmp", d + "/token")
+a.wait_signal(2, timeout_ms=30000)                    # two puts from the peer application
+t = a.local_tensor()
+ok = bool((t[: 1 << 19] == 0x5A).all()) and bool((t[1 << 19 :] == 0xA5).all())
+attached = a.attach_count
+a.free()
+open(d + "/freed", "w").write("1")
+while not os.path.exists(d + "/peer_done"): time.sleep(0.01)
+s = ocm.stats()
+ocm.tini()
+print("RESULT " + json.dumps({"ok": ok, "attached": attached, "live": s["allocs_live"]}))
+"""
+
+SHARE_PEER = r"""
+import json, os, time, torch
+import oncilla_b200 as ocm
+d = os.environ["SHARE_DIR"]
+ocm.init()
+while not os.path.exists(d + "/token"): time.sleep(0.01)
+att = ocm.attach(open(d + "/token", "rb").read())
+info = {"kind": att.kind, "remote_bytes": att.remote_bytes, "remote_rank": att.remote_rank, "is_remote": att.is_remote}
+src = ocm.alloc(ocm.OCM_LOCAL_HOST, 1 << 20)
+t = src.local_tensor(); t[: 1 << 19] = 0x5A; t[1 << 19 :] = 0xA5
+ocm.copy(att, src, 1 << 19)
+ocm.copy(att, src, 1 << 19, src_offset=1 << 19, dest_offset=1 << 19)
+info["signal"] = att.signal()
+try:
+    ocm.copy(att, src, (1 << 20) + 1)
+    info["range"] = "accepted"
+except ocm.OcmError as e:
+    info["range"] = e.err
+while not os.path.exists(d + "/freed"): time.sleep(0.01)
+try:
+    ocm.copy(att, src, 4096)
+    info["after_free"] = "accepted"
+except ocm.OcmError as e:
+    info["after_free"] = e.err
+try:
+    ocm.attach(open(d + "/token", "rb").read())
+    info["reattach"] = "accepted"
+except ocm.OcmError as e:
+    info["reattach"] = e.err
+att.free(); src.free()
+open(d + "/peer_done", "w").write("1")
+ocm.tini()
+print("RESULT " + json.dumps(info))
+"""
+
+
+def test_share_and_attach_between_applications(cluster2, tmp_path):
+    """An application on rank 1 opens a block owned by an application on rank 0, writes it with two copies,
+    and the owner's signal wait sees them; after the owner's free the attached handle is stale."""
+    env = cluster2.env(0)
+    env["PYTHONPATH"] = str(REPO) + os.pathsep + env.get("PYTHONPATH", "")
+    env["SHARE_DIR"] = str(tmp_path)
+    owner = subprocess.Popen([sys.executable, "-c", SHARE_OWNER], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                             text=True)
+    try:
+        peer = _ok(run_py(cluster2, 1, SHARE_PEER, env_extra={"SHARE_DIR": str(tmp_path)}))
+        out, err = owner.communicate(timeout=60)
+    finally:
+        if owner.poll() is None:
+            owner.kill()
+    assert owner.returncode == 0, err
+    o = json.loads(out.split("RESULT ", 1)[1])
+    p = json.loads(peer.split("RESULT ", 1)[1])
+    assert o == {"ok": True, "attached": 1, "live": 0}
+    assert p["kind"] == ocm.OCM_REMOTE_HOST and p["remote_bytes"] == 1 << 20 and p["remote_rank"] == 0 and p["is_remote"]
+    assert p["signal"] == 2
+    assert p["range"] == 5                                  # OCM_ERANGE
+    assert p["after_free"] == 8 and p["reattach"] == 8      # OCM_ESTALE
 
 
 def test_three_ranks_slow_path_forwarding():

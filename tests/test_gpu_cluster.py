@@ -263,9 +263,45 @@ def test_nvls_multicast_replicated_put(gpu_cluster):
     b.free()
 
 
+ATTACH_PEER = r"""
+import sys, torch
+import oncilla_b200 as ocm
+from oncilla_b200 import ops
+ocm.init()
+torch.cuda.set_device(ocm.device())
+att = ocm.attach(bytes.fromhex(sys.argv[1]))
+n = att.remote_bytes
+src = ocm.alloc(ocm.OCM_LOCAL_GPU, n)
+ops.fill(src.local_tensor(), 0xFEEDFACE12345678)
+torch.cuda.synchronize()
+ocm.copy(att, src, n // 2)                                   # two puts -> the owner's signal reaches 2
+ocm.copy(att, src, n - n // 2, src_offset=n // 2, dest_offset=n // 2)
+assert att.signal() == 2 and att.kind == ocm.OCM_REMOTE_GPU
+att.free(); src.free(); ocm.tini()
+print("PEER_OK")
+"""
+
+
+def test_attach_from_another_application(gpu_cluster):
+    """A second application (on the last rank: another GPU when there is one) opens a block of this process
+    by token and writes it with our put kernel; the owner waits on the block's completion signal."""
+    n = (8 << 20) + 4096
+    a = ocm.alloc(ocm.OCM_LOCAL_GPU, n)
+    me = ocm.attach(a.share())                                # same process: aliases the same memory
+    assert me.remote_ptr == a.local_ptr and a.attach_count == 1
+    me.free()
+    assert a.attach_count == 0
+    r = run_py(gpu_cluster, gpu_cluster.n_ranks - 1, ATTACH_PEER, argv=[a.share().hex()])
+    assert r.returncode == 0 and "PEER_OK" in r.stdout, r.stdout + r.stderr
+    a.wait_signal(2, timeout_ms=10000)
+    assert ops.verify(a.local_tensor(), 0xFEEDFACE12345678, n) == 0
+    assert a.attach_count == 0
+    a.free()
+
+
 def test_native_ocm_test_program_gpu(gpu_cluster):
     for args in (["1", "4", "4", "2"], ["1", "4", "8", "7"], ["2", "4", "4", "7"], ["3", "2", "2", "7"],
-                 ["4", "1", "1", "7", "3"]):
+                 ["4", "1", "1", "7", "3"], ["5", "4", "4", "2"], ["5", "4", "4", "7"]):
         r = run_app(gpu_cluster, 0, [BIN / "ocm_test", *args])
         assert r.returncode == 0, r.stdout + r.stderr
         assert "pass: OCM test completed successfully" in r.stdout
@@ -281,6 +317,32 @@ def test_workloads_gups_and_sort(gpu_cluster):
     # force the host tier: HBM budget of one run per rank
     res = sort.run(total_keys=1 << 20, chunk_keys=1 << 18, gpu_budget_per_rank=(1 << 18) * 8)
     assert res["ok"] and res["bytes_in_host"] > 0
+
+
+def test_distributed_sort_single_rank_and_torchrun(gpu_cluster):
+    """The sample sort over shared blocks: in this process (world 1), then as a torchrun job with one
+    application per GPU (2 ranks when there are two GPUs) that exchanges keys with one-sided puts."""
+    import os
+    import sys
+
+    from conftest import REPO
+    from oncilla_b200.models import dsort
+
+    res = dsort.run(keys_per_rank=1 << 18)
+    assert res["ok"] and res["recv_keys"] == 1 << 18
+    n = min(torch.cuda.device_count(), 2)
+    env = {k: v for k, v in os.environ.items() if not k.startswith("OCM_")}
+    env["PYTHONPATH"] = str(REPO) + os.pathsep + env.get("PYTHONPATH", "")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+                        "--master-addr", "127.0.0.1", "--master-port", "29631", str(REPO / "bench" / "workloads.py"),
+                        "--only", "dsort", "--dsort-keys", str(1 << 20)], env=env, capture_output=True, text=True,
+                       timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    line = [l for l in r.stdout.splitlines() if '"distributed_sort"' in l][-1]
+    import json
+
+    out = json.loads(line)
+    assert out["verified"] is True and out["n_gpus"] == n
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
