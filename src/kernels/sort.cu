@@ -1,14 +1,16 @@
 // K8 - device building block of the out-of-core sort pipeline (BASELINE.json
 // config 4): stable LSD radix sort of 64-bit keys, 8 bits per pass.
 // No counterpart in the reference (it ships no compute at all).
-// Per pass: (1) per-CTA digit histograms into global scratch, (2) one-CTA
+// Per pass: (1) per-CTA digit histograms into global scratch, (2) two-step
 // exclusive scan in digit-major order, (3) stable scatter - every CTA walks its
-// contiguous chunk in order, 256 keys per round, ranking equal digits with warp
-// match masks and a warp-sequential hand-over of the running digit offsets.
-// The partition exchange between GPUs is K1/K4 (oncilla_b200/models/sort.py).
+// contiguous chunk in tiles, ranks equal digits with warp match masks, sorts the
+// tile by digit in shared memory and stores whole digit runs.
+// The partition exchange between GPUs is K1/K4 (oncilla_b200/models/sort.py,
+// oncilla_b200/models/dsort.py).
 #include "kernels.h"
 #include "ptx.cuh"
 #include <algorithm>
+#include <cstdlib>
 
 namespace ocmk {
 
@@ -17,6 +19,20 @@ constexpr int kRadix = 256;
 
 __device__ __forceinline__ uint32_t digit_of(uint64_t k, int shift) { return (uint32_t)(k >> shift) & 0xffu; }
 
+// Lanes of the warp whose 8-bit digit equals mine, from eight ballots.  __match_any_sync gives the same
+// mask in one instruction, but MATCH.ANY occupies the SM's single address-divergence unit for ~64 cycles
+// per warp: with it the scatter kernel ran that pipe at 80 % and nothing else mattered (profiles/README.md 7f).
+__device__ __forceinline__ uint32_t match_digit8(uint32_t d) {
+    uint32_t peers = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        const bool bit = (d >> b) & 1u;
+        const uint32_t m = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? m : ~m;
+    }
+    return peers;
+}
+
 // counts[d * n_ctas + cta]
 __global__ void __launch_bounds__(kSortThreads) ocm_sort_hist_kernel(const uint64_t *keys, uint64_t n, int shift,
                                                                      uint32_t *counts, uint64_t chunk) {
@@ -24,7 +40,32 @@ __global__ void __launch_bounds__(kSortThreads) ocm_sort_hist_kernel(const uint6
     h[threadIdx.x] = 0;
     __syncthreads();
     const uint64_t lo = (uint64_t)blockIdx.x * chunk, hi = lo + chunk < n ? lo + chunk : n;
-    for (uint64_t i = lo + threadIdx.x; i < hi; i += kSortThreads) atomicAdd(&h[digit_of(keys[i], shift)], 1u);
+    if ((reinterpret_cast<uintptr_t>(keys + lo) & 15) != 0) {   // odd base pointer: one key per load
+        for (uint64_t i = lo + threadIdx.x; i < hi; i += kSortThreads) atomicAdd(&h[digit_of(keys[i], shift)], 1u);
+        __syncthreads();
+        counts[(uint64_t)threadIdx.x * gridDim.x + blockIdx.x] = h[threadIdx.x];
+        return;
+    }
+    // 16-byte aligned chunk: two keys per load, four loads in flight
+    const uint64_t pairs = hi > lo ? (hi - lo) / 2 : 0;
+    const ulonglong2 *kp = reinterpret_cast<const ulonglong2 *>(keys + lo);
+    uint64_t p = threadIdx.x;
+    for (; p + 3 * kSortThreads < pairs; p += 4 * kSortThreads) {
+        ulonglong2 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = kp[p + u * kSortThreads];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            atomicAdd(&h[digit_of(v[u].x, shift)], 1u);
+            atomicAdd(&h[digit_of(v[u].y, shift)], 1u);
+        }
+    }
+    for (; p < pairs; p += kSortThreads) {
+        const ulonglong2 v = kp[p];
+        atomicAdd(&h[digit_of(v.x, shift)], 1u);
+        atomicAdd(&h[digit_of(v.y, shift)], 1u);
+    }
+    if (threadIdx.x == 0 && hi > lo && ((hi - lo) & 1)) atomicAdd(&h[digit_of(keys[hi - 1], shift)], 1u);
     __syncthreads();
     counts[(uint64_t)threadIdx.x * gridDim.x + blockIdx.x] = h[threadIdx.x];
 }
@@ -79,61 +120,120 @@ __global__ void __launch_bounds__(256) ocm_sort_scan_digits_kernel(const uint64_
     digit_base[threadIdx.x] = block_exclusive_scan_256(row_total[threadIdx.x], &total, warp_sums);
 }
 
-__global__ void __launch_bounds__(kSortThreads) ocm_sort_scatter_kernel(const uint64_t *in, uint64_t *out, uint64_t n,
-                                                                        int shift, const uint64_t *offsets,
-                                                                        const uint64_t *digit_base, uint64_t chunk) {
-    // One round = kKeysPerThread x 256 keys, taken in index order as "slots" (sub-round j, warp w):
-    // slot s = j * 8 + w holds the keys  base + j*256 + w*32 + lane.
-    //   1. every warp counts its keys per digit (match masks), leaders write cnt[slot][digit]
-    //   2. thread d turns cnt[.][d] into an exclusive prefix over the 32 slots and advances off[d]
-    //   3. every key goes to off_old[d] + prefix[slot][d] + rank inside its warp
-    // Three barriers per 1024 keys (the first version handed the running offsets from warp to warp and
-    // paid eight barriers per 256 keys).  cnt is double-buffered so that clearing overlaps the scatter.
-    constexpr int kKeysPerThread = 4;
+// Stable scatter.  A CTA walks its chunk in tiles of kSortThreads * IPT keys; warp w owns the w-th
+// contiguous 32*IPT keys of the tile (item j of lane l = key w*32*IPT + j*32 + l, i.e. index order).
+//   1. ranking: per item, lanes with equal digits find each other (eight ballots); the lowest one
+//      advances the warp's running counter cnt[w][digit] in shared memory and broadcasts the old value
+//      -> rank of every key among the keys of its digit inside its warp, no block barrier involved.
+//      The ballots of all items are issued first (independent of each other), the counter hand-over
+//      follows as a second, sequential sweep.
+//   2. thread d turns cnt[.][d] into a prefix over the warps; a block scan over the digit totals gives
+//      the tile-local start of every digit (tprefix) and advances the CTA's global cursors (off)
+//   3. keys are first placed in shared memory at their tile-local sorted position, then written out in
+//      that order: consecutive threads store consecutive addresses inside each digit run, so the global
+//      stores are whole sectors instead of 8-byte fragments (avg run = tile/256 keys)
+// The next tile's keys are requested as soon as the registers are free (after the placement), so the
+// load latency hides behind the write-out.  Four barriers per tile; every warp clears its own counter row.
+// (History: version 1 handed the running offsets from warp to warp, eight barriers per 256 keys; version 2
+// ranked 1024 keys with three barriers but scattered straight from registers, 8 bytes per sector; version 3
+// used __match_any_sync, which saturates the SM's address-divergence unit.)
+template <int IPT>
+__global__ void __launch_bounds__(kSortThreads, IPT <= 8 ? 4 : 2)
+    ocm_sort_scatter_kernel(const uint64_t *in, uint64_t *out, uint64_t n, int shift, const uint64_t *offsets,
+                            const uint64_t *digit_base, uint64_t chunk) {
     constexpr int kWarps = kSortThreads / 32;
-    constexpr int kSlots = kKeysPerThread * kWarps;
-    __shared__ uint64_t off[2][kRadix];
-    __shared__ uint16_t cnt[2][kSlots][kRadix];
-    off[0][threadIdx.x] = digit_base[threadIdx.x] + offsets[(uint64_t)threadIdx.x * gridDim.x + blockIdx.x];
-    for (int i = threadIdx.x; i < kSlots * kRadix; i += kSortThreads) (&cnt[0][0][0])[i] = 0;
-    __syncthreads();
+    constexpr int kTile = kSortThreads * IPT;
+    __shared__ uint64_t skeys[kTile];
+    __shared__ uint64_t off[kRadix];      // next global position of digit d for this CTA
+    __shared__ uint64_t gpos[kRadix];     // global position of tile-local index 0 as seen from digit d
+    __shared__ uint32_t cnt[kWarps][kRadix];
+    __shared__ uint32_t tprefix[kRadix];
+    __shared__ uint32_t wsum[kWarps];
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const uint32_t lt_mask = (1u << lane) - 1;
+    off[t] = digit_base[t] + offsets[(uint64_t)t * gridDim.x + blockIdx.x];
+#pragma unroll
+    for (int i = 0; i < kRadix / 32; ++i) cnt[warp][lane + 32 * i] = 0;
     const uint64_t lo = (uint64_t)blockIdx.x * chunk, hi = lo + chunk < n ? lo + chunk : n;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int buf = 0;
-    for (uint64_t base = lo; base < hi; base += (uint64_t)kSortThreads * kKeysPerThread, buf ^= 1) {
-        uint64_t k[kKeysPerThread];
-        uint32_t d[kKeysPerThread], rank[kKeysPerThread];
-        bool valid[kKeysPerThread];
+    const uint64_t woff = (uint64_t)warp * 32 * IPT + lane;   // my first key inside a tile
+    uint64_t k[IPT];
 #pragma unroll
-        for (int j = 0; j < kKeysPerThread; ++j) {
-            const uint64_t i = base + (uint64_t)j * kSortThreads + threadIdx.x;
-            valid[j] = i < hi;
-            k[j] = valid[j] ? in[i] : 0;
-            d[j] = digit_of(k[j], shift);
-            // lanes of this warp holding the same digit (invalid lanes get a private class)
-            const uint32_t peers = __match_any_sync(0xffffffffu, valid[j] ? d[j] : 0x100u + lane);
-            rank[j] = __popc(peers & ((1u << lane) - 1));
-            if (valid[j] && rank[j] == 0) cnt[buf][j * kWarps + warp][d[j]] = (uint16_t)__popc(peers);
+    for (int j = 0; j < IPT; ++j) k[j] = lo + woff + j * 32 < hi ? in[lo + woff + j * 32] : ~0ull;
+    __syncwarp();
+    for (uint64_t base = lo; base < hi; base += kTile) {
+        // items of this lane that exist (only the last tile of a chunk is short)
+        const uint64_t left = hi - base;
+        const int nv = left >= (uint64_t)kTile ? IPT
+                       : (left > woff ? (int)((left - woff + 31) / 32 < (uint64_t)IPT ? (left - woff + 31) / 32 : IPT) : 0);
+        uint32_t pr[IPT];   // peers, then rank
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) {
+            // lanes of this warp holding the same digit; lanes past the end of the chunk stand alone
+            const uint32_t vmask = __ballot_sync(0xffffffffu, j < nv);
+            const uint32_t same = match_digit8(digit_of(k[j], shift)) & vmask;
+            pr[j] = j < nv ? same : (1u << lane);
         }
-        __syncthreads();
-        {   // thread t owns digit t
-            const int t = threadIdx.x;
-            uint32_t run = 0;
-#pragma unroll 8
-            for (int s = 0; s < kSlots; ++s) {
-                const uint32_t c = cnt[buf][s][t];
-                cnt[buf][s][t] = (uint16_t)run;
-                run += c;
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) {
+            const uint32_t peers = pr[j];
+            const int leader = __ffs(peers) - 1;
+            uint32_t before = 0;
+            if (j < nv && lane == leader) {
+                const uint32_t d = digit_of(k[j], shift);
+                before = cnt[warp][d];
+                cnt[warp][d] = before + __popc(peers);
             }
-            off[buf ^ 1][t] = off[buf][t] + run;
+            __syncwarp();   // the next item's leader may be another lane reading this counter
+            pr[j] = __shfl_sync(0xffffffffu, before, leader) + __popc(peers & lt_mask);
         }
-        // clear the other buffer for the next round (nobody reads it any more: the barrier above is past its scatter)
-        for (int i = threadIdx.x; i < kSlots * kRadix; i += kSortThreads) (&cnt[buf ^ 1][0][0])[i] = 0;
+        __syncthreads();
+        // thread t owns digit t: prefix over the warps, then a block scan over the digits
+        uint32_t run = 0;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) {
+            const uint32_t c = cnt[w][t];
+            cnt[w][t] = run;
+            run += c;
+        }
+        uint32_t inc = run;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += v;
+        }
+        if (lane == 31) wsum[warp] = inc;
+        __syncthreads();
+        uint32_t ex = inc - run;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w)
+            if (w < warp) ex += wsum[w];
+        tprefix[t] = ex;
+        gpos[t] = off[t] - ex;
+        off[t] += run;
         __syncthreads();
 #pragma unroll
-        for (int j = 0; j < kKeysPerThread; ++j)
-            if (valid[j]) out[off[buf][d[j]] + cnt[buf][j * kWarps + warp][d[j]] + rank[j]] = k[j];
+        for (int j = 0; j < IPT; ++j)
+            if (j < nv) {
+                const uint32_t d = digit_of(k[j], shift);
+                skeys[tprefix[d] + cnt[warp][d] + pr[j]] = k[j];
+            }
+        // the registers are free: request the next tile now, clear my warp's counter row for it
+        const uint64_t nb = base + kTile + woff;
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) k[j] = nb + j * 32 < hi ? in[nb + j * 32] : ~0ull;
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < kRadix / 32; ++i) cnt[warp][lane + 32 * i] = 0;
         __syncthreads();
+        const uint32_t tile_n = left < (uint64_t)kTile ? (uint32_t)left : (uint32_t)kTile;
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) {
+            const uint32_t i = t + j * kSortThreads;
+            if (i < tile_n) {
+                const uint64_t kk = skeys[i];
+                out[gpos[digit_of(kk, shift)] + i] = kk;
+            }
+        }
     }
 }
 
@@ -156,12 +256,17 @@ static void sort_passes(uint64_t *keys, uint64_t *tmp, uint64_t n, int ctas, voi
     uint64_t *digit_base = row_total + kRadix;
     const uint64_t chunk = ((n + ctas - 1) / ctas + kSortThreads - 1) / kSortThreads * kSortThreads;
     uint64_t *a = keys, *b = tmp;
+    static const int ipt = [] {
+        const char *e = getenv("OCM_SORT_IPT");   // keys per thread per tile of the scatter: 8 (default) or 16
+        return e && atoi(e) == 16 ? 16 : 8;
+    }();
     for (int pass = 0; pass < 8; ++pass) {
         const int shift = pass * 8;
         ocm_sort_hist_kernel<<<ctas, kSortThreads, 0, stream>>>(a, n, shift, counts, chunk);
         ocm_sort_scan_rows_kernel<<<kRadix, 256, 0, stream>>>(counts, offsets, row_total, ctas);
         ocm_sort_scan_digits_kernel<<<1, 256, 0, stream>>>(row_total, digit_base);
-        ocm_sort_scatter_kernel<<<ctas, kSortThreads, 0, stream>>>(a, b, n, shift, offsets, digit_base, chunk);
+        if (ipt == 16) ocm_sort_scatter_kernel<16><<<ctas, kSortThreads, 0, stream>>>(a, b, n, shift, offsets, digit_base, chunk);
+        else ocm_sort_scatter_kernel<8><<<ctas, kSortThreads, 0, stream>>>(a, b, n, shift, offsets, digit_base, chunk);
         std::swap(a, b);
     }
 }
