@@ -35,9 +35,11 @@ __device__ __forceinline__ uint32_t match_digit8(uint32_t d) {
 
 // counts[d * n_ctas + cta]
 __global__ void __launch_bounds__(kSortThreads) ocm_sort_hist_kernel(const uint64_t *keys, uint64_t n, int shift,
-                                                                     uint32_t *counts, uint64_t chunk) {
+                                                                     uint32_t *counts, uint64_t chunk,
+                                                                     unsigned int *scan_ticket) {
     __shared__ uint32_t h[kRadix];
     h[threadIdx.x] = 0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *scan_ticket = 0;   // for the scan kernel that follows in the stream
     __syncthreads();
     const uint64_t lo = (uint64_t)blockIdx.x * chunk, hi = lo + chunk < n ? lo + chunk : n;
     if ((reinterpret_cast<uintptr_t>(keys + lo) & 15) != 0) {   // odd base pointer: one key per load
@@ -70,10 +72,10 @@ __global__ void __launch_bounds__(kSortThreads) ocm_sort_hist_kernel(const uint6
     counts[(uint64_t)threadIdx.x * gridDim.x + blockIdx.x] = h[threadIdx.x];
 }
 
-// Exclusive scan of the digit-major count matrix in two small steps (a single-CTA scan of all
-// 256 x ctas entries took 253 us per pass - more than the histogram and the scatter together):
+// Exclusive scan of the digit-major count matrix in two small steps inside one kernel (a single-CTA
+// scan of all 256 x ctas entries took 253 us per pass - more than the histogram and the scatter together):
 //   rows:   CTA d scans row d (one entry per scatter CTA) -> offsets[d][cta] relative to the row, row_total[d]
-//   digits: one CTA scans the 256 row totals -> digit_base[d]
+//   digits: the CTA that finishes last (ticket) scans the 256 row totals -> digit_base[d]
 // The scatter kernel starts bucket d of CTA c at digit_base[d] + offsets[d][c].
 __device__ __forceinline__ uint64_t block_exclusive_scan_256(uint64_t v, uint64_t *total, uint64_t *warp_sums) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -97,9 +99,10 @@ __device__ __forceinline__ uint64_t block_exclusive_scan_256(uint64_t v, uint64_
     return base + inc - v;
 }
 
-__global__ void __launch_bounds__(256) ocm_sort_scan_rows_kernel(const uint32_t *counts, uint64_t *offsets,
-                                                                 uint64_t *row_total, int ctas) {
+__global__ void __launch_bounds__(256) ocm_sort_scan_kernel(const uint32_t *counts, uint64_t *offsets, uint64_t *row_total,
+                                                            uint64_t *digit_base, int ctas, unsigned int *ticket) {
     __shared__ uint64_t warp_sums[8];
+    __shared__ bool last;
     const uint32_t *row = counts + (uint64_t)blockIdx.x * ctas;
     uint64_t *orow = offsets + (uint64_t)blockIdx.x * ctas;
     uint64_t carry = 0;
@@ -111,13 +114,16 @@ __global__ void __launch_bounds__(256) ocm_sort_scan_rows_kernel(const uint32_t 
         if (i < ctas) orow[i] = carry + ex;
         carry += total;
     }
-    if (threadIdx.x == 0) row_total[blockIdx.x] = carry;
-}
-
-__global__ void __launch_bounds__(256) ocm_sort_scan_digits_kernel(const uint64_t *row_total, uint64_t *digit_base) {
-    __shared__ uint64_t warp_sums[8];
+    if (threadIdx.x == 0) {
+        row_total[blockIdx.x] = carry;
+        __threadfence();                                       // my total is visible before my ticket
+        last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();                                           // every other CTA's total is visible now
     uint64_t total;
-    digit_base[threadIdx.x] = block_exclusive_scan_256(row_total[threadIdx.x], &total, warp_sums);
+    digit_base[threadIdx.x] = block_exclusive_scan_256(__ldcg(row_total + threadIdx.x), &total, warp_sums);
 }
 
 // Stable scatter.  A CTA walks its chunk in tiles of kSortThreads * IPT keys; warp w owns the w-th
@@ -237,23 +243,26 @@ __global__ void __launch_bounds__(kSortThreads, IPT <= 8 ? 4 : 2)
     }
 }
 
-// scratch layout: counts u32[256][ctas] | offsets u64[256][ctas] | row_total u64[256] | digit_base u64[256]
+// scratch layout: counts u32[256][ctas] | offsets u64[256][ctas] | row_total u64[256] | digit_base u64[256] | ticket
+// (the ticket word is reset by each pass's histogram kernel: nothing in the scratch has to start at zero)
 constexpr size_t sort_scratch_for(int ctas) {
-    return (size_t)kRadix * ctas * (sizeof(uint32_t) + sizeof(uint64_t)) + 2 * (size_t)kRadix * sizeof(uint64_t);
+    return (size_t)kRadix * ctas * (sizeof(uint32_t) + sizeof(uint64_t)) + 2 * (size_t)kRadix * sizeof(uint64_t) + 8;
 }
 
 size_t sort_scratch_bytes(uint64_t n, int *ctas_out) {
-    int ctas = (int)std::min<uint64_t>(std::max<uint64_t>((n + 8191) / 8192, 1), (uint64_t)num_sms() * 4);
+    // one scatter tile (2048 keys) per CTA until the grid is four CTAs per SM, longer chunks after that
+    int ctas = (int)std::min<uint64_t>(std::max<uint64_t>((n + 2047) / 2048, 1), (uint64_t)num_sms() * 4);
     if (ctas_out) *ctas_out = ctas;
     return sort_scratch_for(ctas);
 }
 
-// The eight passes (hist, two scan steps, scatter), shared by the regular and the allocation-free entry point.
+// The eight passes (hist, scan, scatter), shared by the regular and the allocation-free entry point.
 static void sort_passes(uint64_t *keys, uint64_t *tmp, uint64_t n, int ctas, void *scratch, cudaStream_t stream) {
     uint32_t *counts = static_cast<uint32_t *>(scratch);
     uint64_t *offsets = reinterpret_cast<uint64_t *>(static_cast<uint8_t *>(scratch) + (size_t)kRadix * ctas * sizeof(uint32_t));
     uint64_t *row_total = offsets + (size_t)kRadix * ctas;
     uint64_t *digit_base = row_total + kRadix;
+    unsigned int *ticket = reinterpret_cast<unsigned int *>(digit_base + kRadix);
     const uint64_t chunk = ((n + ctas - 1) / ctas + kSortThreads - 1) / kSortThreads * kSortThreads;
     uint64_t *a = keys, *b = tmp;
     static const int ipt = [] {
@@ -262,9 +271,8 @@ static void sort_passes(uint64_t *keys, uint64_t *tmp, uint64_t n, int ctas, voi
     }();
     for (int pass = 0; pass < 8; ++pass) {
         const int shift = pass * 8;
-        ocm_sort_hist_kernel<<<ctas, kSortThreads, 0, stream>>>(a, n, shift, counts, chunk);
-        ocm_sort_scan_rows_kernel<<<kRadix, 256, 0, stream>>>(counts, offsets, row_total, ctas);
-        ocm_sort_scan_digits_kernel<<<1, 256, 0, stream>>>(row_total, digit_base);
+        ocm_sort_hist_kernel<<<ctas, kSortThreads, 0, stream>>>(a, n, shift, counts, chunk, ticket);
+        ocm_sort_scan_kernel<<<kRadix, 256, 0, stream>>>(counts, offsets, row_total, digit_base, ctas, ticket);
         if (ipt == 16) ocm_sort_scatter_kernel<16><<<ctas, kSortThreads, 0, stream>>>(a, b, n, shift, offsets, digit_base, chunk);
         else ocm_sort_scatter_kernel<8><<<ctas, kSortThreads, 0, stream>>>(a, b, n, shift, offsets, digit_base, chunk);
         std::swap(a, b);
@@ -278,7 +286,7 @@ cudaError_t launch_sort_u64(uint64_t *keys, uint64_t *tmp, uint64_t n, void *scr
     int ctas = 0;
     if (scratch_bytes < sort_scratch_bytes(n, &ctas)) return cudaErrorInvalidValue;
     sort_passes(keys, tmp, n, ctas, scratch, stream);
-    if (launches) *launches += 8 * 4;
+    if (launches) *launches += 8 * 3;
     return cudaGetLastError();
 }
 
@@ -305,7 +313,8 @@ cudaError_t launch_sort_u64(uint64_t *keys, uint64_t *tmp, uint64_t n, void *scr
 //     entry point runs on that device.  Make that first call before starting any stream capture;
 //   * all calls on a device share the one array, which keeps whatever the previous call left in
 //     it.  Nothing in it has to start at zero: every pass rewrites each histogram and offset
-//     entry before reading it, so there is nothing to clear between calls;
+//     entry before reading it and its histogram kernel resets the scan ticket word, so there is
+//     nothing to clear between calls;
 //   * because the array is shared, two calls whose kernels overlap on the same GPU (different
 //     streams, or different host threads) race on it and produce garbage - serialise them;
 //   * no cudaMalloc, cudaFree or other allocating call is made here; keys and tmp (n elements
