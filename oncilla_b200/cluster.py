@@ -111,14 +111,27 @@ class TorchrunCluster:
         return self.rank, self.world
 
     def __exit__(self, *exc):
-        import torch.distributed as dist
-
         from . import api
 
+        if exc and exc[0] is not None:
+            # A rank that failed must not wait for the others in a barrier they will never reach (that hides
+            # the error behind a hang): report, stop our daemon and leave - torchrun then tears the job down.
+            import sys
+            import traceback
+
+            traceback.print_exception(*exc)
+            sys.stderr.flush()
+            try:
+                api.tini()
+            finally:
+                self.cl.stop()
+                os._exit(1)
         api.tini()
         self.barrier()
         self.cl.stop()
         if self.world > 1:
+            import torch.distributed as dist
+
             dist.destroy_process_group()
 
 

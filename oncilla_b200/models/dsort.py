@@ -58,6 +58,7 @@ def run(keys_per_rank: int = 1 << 22, check: bool = True, seed: int = 0xD5EED, o
     in_sum = ops.checksum(wt) if check else 0
     recv = rtmp = None
     peers = []
+    finished = False
     try:
         barrier()
         t0 = time.perf_counter()
@@ -90,7 +91,7 @@ def run(keys_per_rank: int = 1 << 22, check: bool = True, seed: int = 0xD5EED, o
                 off = int(cmat[:rank, dst].sum())
                 api.copy(peers[dst], work, cnt * 8, src_offset=bounds[dst] * 8, dest_offset=off * 8, stream=st)
         # 5. wait for every sender's signal on my block, then sort what arrived
-        recv.wait_signal(senders, timeout_ms=60000)
+        recv.wait_signal(senders, timeout_ms=20000)
         t2 = time.perf_counter()
         rt = recv.local_tensor(torch.int64)[:recv_n]
         if recv_n:
@@ -121,6 +122,7 @@ def run(keys_per_rank: int = 1 << 22, check: bool = True, seed: int = 0xD5EED, o
         if dist:
             dist.all_reduce(el, op=dist.ReduceOp.MAX)
         total, sort1, exch, sort2 = el.tolist()
+        finished = True
         return {"world": world, "keys_per_rank": n, "total_keys": n * world, "seconds": total,
                 "local_sort_s": sort1, "exchange_s": exch, "final_sort_s": sort2,
                 "mkeys_per_s": n * world / total / 1e6, "recv_keys": recv_n,
@@ -128,7 +130,8 @@ def run(keys_per_rank: int = 1 << 22, check: bool = True, seed: int = 0xD5EED, o
     finally:
         for p in peers:
             p.free()
-        barrier()                                             # nobody still writes into a block that goes away
+        if finished:                                          # (a failing rank must not wait for the others)
+            barrier()                                         # nobody still writes into a block that goes away
         for a in (recv, rtmp, work, tmp):
             if a is not None:
                 a.free()

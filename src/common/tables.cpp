@@ -181,6 +181,7 @@ size_t table_segment_bytes(uint64_t gpu_pool_bytes, uint64_t host_pool_bytes, ui
         total += round_up(n * sizeof(Region), 4096);
         total += round_up((n + 63) / 64 * 8, 4096);
     }
+    total += round_up((size_t)kSigExtRecords * sizeof(SigExt), 4096);
     return total;
 }
 
@@ -219,6 +220,9 @@ void table_format(void *base, size_t seg_bytes, int rank, int n_ranks, int daemo
             bm[p.bitmap_words - 1].store(~((1ull << (p.n_granules & 63)) - 1), std::memory_order_relaxed);
         }
     }
+    h->sigext_offset = off;
+    h->n_sigext = kSigExtRecords;
+    off += round_up((size_t)kSigExtRecords * sizeof(SigExt), 4096);
     OCM_BUG(off > seg_bytes);
 }
 
@@ -233,10 +237,49 @@ bool table_validate(const TableHeader *h, size_t mapped) {
         if (p.bitmap_offset + (uint64_t)p.bitmap_words * 8 > mapped) return false;
         if (p.granule & (p.granule - 1)) return false;
     }
+    if (h->sigext_offset + (uint64_t)h->n_sigext * sizeof(SigExt) > mapped) return false;
     return true;
 }
 
 // ------------------------------------------------------------- allocator --
+// ---------------------------------------------------- signal extensions --
+SigExt *sigext_claim(TableHeader *h, int tier, uint32_t region) {
+    Region &r = table_regions(h, tier)[region];
+    SigExt *ext = table_sigext(h);
+    uint32_t have = r.ext.load(std::memory_order_acquire);
+    if (have) return &ext[have - 1];
+    const uint64_t tag = (((uint64_t)tier << 32) | region) + 1;
+    for (uint32_t i = 0; i < h->n_sigext; ++i) {
+        uint64_t expect = 0;
+        if (ext[i].owner.load(std::memory_order_relaxed) != 0 ||
+            !ext[i].owner.compare_exchange_strong(expect, tag, std::memory_order_acq_rel))
+            continue;
+        ext[i].id = r.id;
+        for (auto &s : ext[i].slot) s.store(0, std::memory_order_relaxed);
+        uint32_t none = 0;
+        if (r.ext.compare_exchange_strong(none, i + 1, std::memory_order_acq_rel)) return &ext[i];
+        ext[i].owner.store(0, std::memory_order_release);   // another thread of the owner won
+        return &ext[none - 1];
+    }
+    return nullptr;
+}
+
+// the block leaves the LIVE state: its extension record (if any) becomes free again
+static void sigext_release(TableHeader *h, Region &r) {
+    const uint32_t e = r.ext.exchange(0, std::memory_order_acq_rel);
+    if (e && e <= h->n_sigext) table_sigext(h)[e - 1].owner.store(0, std::memory_order_release);
+}
+
+uint64_t region_signal_total(TableHeader *h, const Region &r) {
+    uint64_t v = r.signal.load(std::memory_order_acquire) + r.signal_cpu.load(std::memory_order_acquire);
+    const uint32_t e = r.ext.load(std::memory_order_acquire);
+    if (e && e <= h->n_sigext) {
+        const SigExt &x = table_sigext(h)[e - 1];
+        for (const auto &s : x.slot) v += s.load(std::memory_order_acquire);
+    }
+    return v;
+}
+
 int pool_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int rank, BlockRef *out) {
     if (tier < 0 || tier >= TIER_COUNT || !out) return OCM_EINVAL;
     PoolDesc &p = h->pool[tier];
@@ -262,9 +305,10 @@ int pool_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int rank, Bloc
     r.bytes = bytes;
     r.id = h->next_id.fetch_add(1, std::memory_order_relaxed);
     r.generation += 1;
-    r.flags = 0;
     r.attached.store(0, std::memory_order_relaxed);
+    r.ext.store(0, std::memory_order_relaxed);
     r.signal.store(0, std::memory_order_relaxed);
+    r.signal_cpu.store(0, std::memory_order_relaxed);
     r.state.store(REGION_LIVE, std::memory_order_release);
     p.used_bytes.fetch_add(block_bytes, std::memory_order_relaxed);
     p.live.fetch_add(1, std::memory_order_relaxed);
@@ -289,6 +333,7 @@ int pool_free(TableHeader *h, int tier, uint32_t region, uint64_t id) {
     uint32_t expect = REGION_LIVE;
     if (!r.state.compare_exchange_strong(expect, scrub ? REGION_DIRTY : REGION_FREE, std::memory_order_acq_rel))
         return OCM_ESTALE; // lost a race with another free / the reclaimer
+    sigext_release(h, r);
     const uint64_t block_bytes = (uint64_t)n * p.granule;
     p.used_bytes.fetch_sub(block_bytes, std::memory_order_relaxed);
     p.live.fetch_sub(1, std::memory_order_relaxed);

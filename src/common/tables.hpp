@@ -33,7 +33,7 @@
 namespace ocm {
 
 constexpr uint64_t kTableMagic   = 0x4F434D5441424C45ull; // "OCMTABLE"
-constexpr uint32_t kTableVersion = 5;
+constexpr uint32_t kTableVersion = 6;
 constexpr uint32_t kMaxGranules  = 1u << 18;
 constexpr uint64_t kMcGranule     = 64ull << 10;
 constexpr uint32_t kMcMaxGranules = 1u << 14;     // multicast region <= 1 GiB
@@ -50,12 +50,28 @@ struct alignas(64) Region {
     int32_t               owner_rank;
     uint64_t              bytes;       // requested bytes
     uint64_t              id;          // rem_alloc_id
-    std::atomic<uint64_t> signal;      // completion counter (puts add 1)
-    uint64_t              flags;
+    std::atomic<uint64_t> signal;      // completion counter: puts issued by the OWNER's GPU add 1
+    std::atomic<uint64_t> signal_cpu;  //   "      "     : copies done by CPUs (host <-> host) add 1
     std::atomic<uint32_t> attached;    // handles other applications hold on this block (ocm_attach)
-    uint32_t              reserved;
+    std::atomic<uint32_t> ext;         // shared blocks: index + 1 of the SigExt record, 0 = none
 };
 static_assert(sizeof(Region) == 64, "one cache line per region");
+
+// Completion counters of a block that is shared between applications (ocm_share / ocm_attach).
+// A system-scope reduction from a GPU to host memory is only atomic with respect to the SAME GPU on boxes
+// without PCIe atomics (cudaDevAttrHostNativeAtomicSupported = 0 on the B200 HGX boxes: four GPUs adding
+// to one pinned word lost 25 % of the updates, with a CPU thread joining in 75 % - bench/atomics_probe.cu).
+// So every word has exactly one writing agent: slot r is written by the GPU of rank r, the last slot by
+// CPUs (coherent among themselves); the reader adds them up.  The owner's own GPU keeps Region::signal.
+constexpr int kSigGpuSlots = kMaxRanks;
+constexpr int kSigCpuSlot  = kMaxRanks;
+struct alignas(64) SigExt {
+    std::atomic<uint64_t> owner;       // 0 = free, else (tier << 32 | region) + 1
+    uint64_t              id;          // allocation id of the block it serves
+    uint64_t              pad[6];
+    std::atomic<uint64_t> slot[kMaxRanks + 8];
+};
+constexpr uint32_t kSigExtRecords = 1024;
 
 struct PoolDesc {
     uint64_t bytes;            // capacity
@@ -95,6 +111,9 @@ struct TableHeader {
     std::atomic<uint64_t> heartbeat_ns; // daemon liveness (CLOCK_MONOTONIC)
     uint64_t mc_tail_offset;           // NVLS: byte offset inside the HBM pool mapping of the multicast slice
     uint64_t mc_bytes;                 //       its length (0: none)
+    uint64_t sigext_offset;            // SigExt[kSigExtRecords], from segment start
+    uint32_t n_sigext;
+    uint32_t pad2;
     PoolDesc pool[TIER_COUNT];
 };
 
@@ -163,6 +182,13 @@ inline Region *table_regions(TableHeader *h, int tier) {
     return reinterpret_cast<Region *>(reinterpret_cast<char *>(h) + h->pool[tier].regions_offset);
 }
 bool table_validate(const TableHeader *h, size_t mapped_bytes);
+inline SigExt *table_sigext(TableHeader *h) {
+    return reinterpret_cast<SigExt *>(reinterpret_cast<char *>(h) + h->sigext_offset);
+}
+// Give a LIVE block its extension record (idempotent).  Returns the record or nullptr when all are taken.
+SigExt *sigext_claim(TableHeader *h, int tier, uint32_t region);
+// Sum of every completion counter of a block (owner GPU + CPUs + all extension slots).
+uint64_t region_signal_total(TableHeader *h, const Region &r);
 
 // ---- lock-free pool operations (any process) ------------------------------
 struct BlockRef {

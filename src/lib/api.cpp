@@ -277,6 +277,9 @@ static int alloc_side(uint32_t type, uint64_t bytes, int policy, int explicit_ra
     out->bytes = bytes;
     out->ptr = v ? side_ptr(v, (int)a.tier, a.offset) : nullptr;
     out->rec = v ? &table_regions(v->hdr, (int)a.tier)[a.region] : nullptr;
+    out->hdr = v ? v->hdr : nullptr;
+    out->sig_gpu = out->rec ? &out->rec->signal : nullptr;
+    out->sig_cpu = out->rec ? &out->rec->signal_cpu : nullptr;
     if (!out->ptr) {
         // reserved but not addressable from here (no GPU in this process / mapping failed)
         release_side(*out);
@@ -785,7 +788,7 @@ int ocm_signal_read(ocm_alloc_t a, uint64_t *value) {
     if (!valid_handle(a) || !value) return -OCM_EINVAL;
     const Side &s = (a->paired && a->remote.valid()) ? a->remote : a->local;
     if (!s.rec) return -OCM_EUNSUPPORTED;
-    *value = s.rec->signal.load(std::memory_order_acquire);
+    *value = region_signal_total(s.hdr, *s.rec);
     return 0;
 }
 
@@ -795,7 +798,7 @@ int ocm_signal_wait(ocm_alloc_t a, uint64_t at_least, int timeout_ms) {
     if (!s.rec) return -OCM_EUNSUPPORTED;
     uint64_t deadline = mono_ns() + (uint64_t)(timeout_ms < 0 ? 0 : timeout_ms) * 1000000ull;
     for (unsigned spin = 0;; ++spin) {
-        if (s.rec->signal.load(std::memory_order_acquire) >= at_least) return 0;
+        if (region_signal_total(s.hdr, *s.rec) >= at_least) return 0;
         if (timeout_ms >= 0 && mono_ns() > deadline) return -OCM_ESTALE;
         if (spin > 1000) usleep(20);
     }
@@ -809,10 +812,25 @@ static const Side *shareable_side(ocm_alloc_t a) {
     return (s.backing == SIDE_POOL || s.backing == SIDE_ATTACHED) && s.rec ? &s : nullptr;
 }
 
+// Which SigExt slot this process's GPU writes: the rank whose pool lives on our CUDA device (normally our
+// own rank); a device that belongs to no rank gets one of the spare slots behind the CPU slot.
+static int gpu_slot() {
+    Ctx &c = ctx();
+    if (c.device < 0) return c.rank;
+    for (int k = 0; k < c.n_ranks; ++k) {
+        const int r = (c.rank + k) % c.n_ranks;
+        RankView *v = get_view(r, false);
+        if (v && v->hdr->gpu_index == c.device) return r;
+    }
+    return kSigCpuSlot + 1 + c.device % 7;
+}
+
 int ocm_share(ocm_alloc_t a, struct ocm_share_token *out) {
     if (!valid_handle(a) || !out) return -OCM_EINVAL;
     const Side *s = shareable_side(a);
     if (!s) return -OCM_EUNSUPPORTED;
+    // a shared block gets per-writer completion counters (tables.hpp, SigExt) before anybody can attach
+    if (!sigext_claim(s->hdr, s->tier, s->region)) return -OCM_ENOMEM;
     memset(out, 0, sizeof *out);
     out->id = s->id;
     out->bytes = s->bytes;
@@ -838,8 +856,9 @@ int ocm_attach(const struct ocm_share_token *tok, ocm_alloc_t *out) {
     Region *rec = &table_regions(v->hdr, (int)tok->tier)[tok->region];
     // count ourselves in first, then check that the block is (still) the one the token names
     rec->attached.fetch_add(1, std::memory_order_acq_rel);
+    const uint32_t ext = rec->ext.load(std::memory_order_acquire);
     const bool live = rec->state.load(std::memory_order_acquire) == REGION_LIVE && rec->id == tok->id &&
-                      rec->generation == tok->generation && rec->bytes == tok->bytes;
+                      rec->generation == tok->generation && rec->bytes == tok->bytes && ext && ext <= v->hdr->n_sigext;
     void *ptr = live ? side_ptr(v, (int)tok->tier, (uint64_t)tok->region * pd.granule) : nullptr;
     if (!ptr) {
         attached_dec(rec);
@@ -865,6 +884,11 @@ int ocm_attach(const struct ocm_share_token *tok, ocm_alloc_t *out) {
     s.bytes = tok->bytes;
     s.ptr = ptr;
     s.rec = rec;
+    s.hdr = v->hdr;
+    // our completion counters: the slot of the rank that owns our GPU (one writing GPU per word), the CPU slot
+    SigExt &x = table_sigext(v->hdr)[ext - 1];
+    s.sig_gpu = &x.slot[gpu_slot()];
+    s.sig_cpu = &x.slot[kSigCpuSlot];
     {
         std::lock_guard<std::mutex> g(c.mu);
         c.allocs.insert(a);

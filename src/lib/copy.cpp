@@ -198,14 +198,16 @@ static int single_copy(const Side &dst, uint64_t dst_off, const Side &src, uint6
 static inline bool fits(const Side &s, uint64_t off, uint64_t n) { return n <= s.bytes && off <= s.bytes - n; }
 
 int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2_off, const Side &src, uint64_t src_off,
-              uint64_t bytes, Region *signal_rec, void *stream, bool *used_stream) {
+              uint64_t bytes, const Side *sig, void *stream, bool *used_stream) {
     Ctx &c = ctx();
     if (!dst.ptr || !src.ptr || (dst2 && !dst2->ptr)) return OCM_EINVAL;
     if (!fits(src, src_off, bytes) || !fits(dst, dst_off, bytes) || (dst2 && !fits(*dst2, dst2_off, bytes)))
         return OCM_ERANGE;
     c.n_copies.fetch_add(1, std::memory_order_relaxed);
     c.copy_bytes.fetch_add(bytes, std::memory_order_relaxed);
-    uint64_t *signal = signal_rec ? reinterpret_cast<uint64_t *>(&signal_rec->signal) : nullptr;
+    // completion counters of the side named as destination: one word for our GPU, one for CPUs
+    uint64_t *signal = sig ? sig->gpu_signal() : nullptr;
+    std::atomic<uint64_t> *signal_cpu = sig ? sig->sig_cpu : nullptr;
     cudaStream_t st = (cudaStream_t)(stream ? stream : c.stream);
 
     const bool all_host = src.tier == TIER_HOST && dst.tier == TIER_HOST && (!dst2 || dst2->tier == TIER_HOST);
@@ -217,7 +219,7 @@ int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2
         const char *s = (const char *)src.ptr + src_off;
         memcpy((char *)dst.ptr + dst_off, s, bytes);
         if (dst2) memcpy((char *)dst2->ptr + dst2_off, s, bytes);
-        if (signal_rec) signal_rec->signal.fetch_add(1, std::memory_order_release);
+        if (signal_cpu) signal_cpu->fetch_add(1, std::memory_order_release);
         return OCM_OK;
     }
     if (c.device < 0) return OCM_ENOGPU;
@@ -254,8 +256,8 @@ int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2
             err = cuda_err(ocmk::launch_signal(signal, st), "signal kernel");
             note_other_gpu_op();
             ++c.kernel_launches;
-        } else {
-            signal_rec->signal.fetch_add(1, std::memory_order_release);
+        } else if (signal_cpu) {
+            signal_cpu->fetch_add(1, std::memory_order_release);
         }
     }
     return err;
@@ -306,7 +308,7 @@ static int stripes_xfer(ocm_alloc_t a, bool to_far, const Side &local, uint64_t 
             uint64_t *sigs[8];
             for (size_t r = 0; r < N; ++r) {
                 dsts[r] = (char *)a->stripes[r].ptr + far_off;
-                sigs[r] = a->stripes[r].rec ? reinterpret_cast<uint64_t *>(&a->stripes[r].rec->signal) : nullptr;
+                sigs[r] = a->stripes[r].gpu_signal();
             }
             DeviceGuard dg(c.device);
             cudaError_t e = ocmk::launch_put_replicated(dsts, (int)N, (const char *)local.ptr + local_off, n, sigs,
@@ -319,7 +321,7 @@ static int stripes_xfer(ocm_alloc_t a, bool to_far, const Side &local, uint64_t 
             return cuda_err(e, "replicated put");
         }
         for (size_t r = 0; r < N; ++r) {
-            int err = side_copy(a->stripes[r], far_off, nullptr, 0, local, local_off, n, a->stripes[r].rec, stream, used);
+            int err = side_copy(a->stripes[r], far_off, nullptr, 0, local, local_off, n, &a->stripes[r], stream, used);
             if (err) return err;
         }
         return OCM_OK;
@@ -330,7 +332,7 @@ static int stripes_xfer(ocm_alloc_t a, bool to_far, const Side &local, uint64_t 
         const size_t r = (size_t)(far_off / a->stripe_bytes);
         const uint64_t in = far_off % a->stripe_bytes;
         const uint64_t piece = std::min<uint64_t>(n, a->stripe_bytes - in);
-        int err = to_far ? side_copy(a->stripes[r], in, nullptr, 0, local, local_off, piece, a->stripes[r].rec, stream, used)
+        int err = to_far ? side_copy(a->stripes[r], in, nullptr, 0, local, local_off, piece, &a->stripes[r], stream, used)
                          : side_copy(local, local_off, nullptr, 0, a->stripes[r], in, piece, nullptr, stream, used);
         if (err) return err;
         far_off += piece;
@@ -361,40 +363,40 @@ static int do_copy(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p,
     int err;
     if (!dfar && !sfar) {
         // local -> local (host/GPU in any combination; GPU->GPU is a no-op in the reference)
-        err = side_copy(dst->local, p->dest_offset, nullptr, 0, src->local, p->src_offset, n, dst->local.rec, stream, used);
+        err = side_copy(dst->local, p->dest_offset, nullptr, 0, src->local, p->src_offset, n, &dst->local, stream, used);
     } else if (dfar && !sfar) {
         // local -> pair: hop 1 into the window, hop 2 window -> far side
         if (!dst->local.valid()) {
             // window-less pair: a single hop, src_offset/dest_offset index source/destination
-            err = side_copy(*dfar, p->dest_offset, nullptr, 0, src->local, p->src_offset, n, dfar->rec, stream, used);
+            err = side_copy(*dfar, p->dest_offset, nullptr, 0, src->local, p->src_offset, n, dfar, stream, used);
         } else if (p->src_offset_2 == p->dest_offset) {
             err = side_copy(*dfar, p->dest_offset_2, &dst->local, p->dest_offset, src->local, p->src_offset, n,
-                            dfar->rec, stream, used);
+                            dfar, stream, used);
         } else if (!fits(dst->local, p->src_offset_2, n) || !fits(*dfar, p->dest_offset_2, n)) {
             err = OCM_ERANGE;   // checked up front so that a bad second hop does not leave the first one done
         } else {
             err = side_copy(dst->local, p->dest_offset, nullptr, 0, src->local, p->src_offset, n, nullptr, stream, used);
             if (!err)
-                err = side_copy(*dfar, p->dest_offset_2, nullptr, 0, dst->local, p->src_offset_2, n, dfar->rec, stream, used);
+                err = side_copy(*dfar, p->dest_offset_2, nullptr, 0, dst->local, p->src_offset_2, n, dfar, stream, used);
         }
     } else if (!dfar && sfar) {
         // pair -> local: hop 1 far side -> window, hop 2 window -> destination
         if (!src->local.valid()) {
-            err = side_copy(dst->local, p->dest_offset, nullptr, 0, *sfar, p->src_offset, n, dst->local.rec, stream, used);
+            err = side_copy(dst->local, p->dest_offset, nullptr, 0, *sfar, p->src_offset, n, &dst->local, stream, used);
         } else if (p->src_offset_2 == p->src_offset) {
             err = side_copy(dst->local, p->dest_offset_2, &src->local, p->src_offset, *sfar, p->dest_offset, n,
-                            dst->local.rec, stream, used);
+                            &dst->local, stream, used);
         } else if (!fits(src->local, p->src_offset_2, n) || !fits(dst->local, p->dest_offset_2, n)) {
             err = OCM_ERANGE;
         } else {
             err = side_copy(src->local, p->src_offset, nullptr, 0, *sfar, p->dest_offset, n, nullptr, stream, used);
             if (!err)
-                err = side_copy(dst->local, p->dest_offset_2, nullptr, 0, src->local, p->src_offset_2, n, dst->local.rec,
+                err = side_copy(dst->local, p->dest_offset_2, nullptr, 0, src->local, p->src_offset_2, n, &dst->local,
                                 stream, used);
         }
     } else {
         // pair -> pair: third-party copy far side -> far side (BUG(1) in the reference, src/lib.c:591-594)
-        err = side_copy(*dfar, p->dest_offset, nullptr, 0, *sfar, p->src_offset, n, dfar->rec, stream, used);
+        err = side_copy(*dfar, p->dest_offset, nullptr, 0, *sfar, p->src_offset, n, dfar, stream, used);
     }
     mark_pending(dst, stream, *used);
     mark_pending(src, stream, *used);
@@ -416,7 +418,7 @@ static int do_onesided(ocm_alloc_t a, const struct ocm_params *p, void *stream, 
     }
     if (p->bytes > a->local.bytes) return OCM_ERANGE;   // as the reference (src/lib.c:679,701)
     int err;
-    if (p->op_flag) err = side_copy(*far, p->dest_offset, nullptr, 0, a->local, p->src_offset, p->bytes, far->rec, stream, used);
+    if (p->op_flag) err = side_copy(*far, p->dest_offset, nullptr, 0, a->local, p->src_offset, p->bytes, far, stream, used);
     else err = side_copy(a->local, p->src_offset, nullptr, 0, *far, p->dest_offset, p->bytes, nullptr, stream, used);
     mark_pending(a, stream, *used);
     return err;
@@ -537,16 +539,16 @@ int ocm_copy_in(ocm_alloc_t dst, void *src) {
     const Side *far = far_side(dst);
     if (!far) {
         Side u = user_side(src, dst->local.bytes);
-        err = side_copy(dst->local, 0, nullptr, 0, u, 0, dst->local.bytes, dst->local.rec, nullptr, &used);
+        err = side_copy(dst->local, 0, nullptr, 0, u, 0, dst->local.bytes, &dst->local, nullptr, &used);
     } else if (!dst->local.valid()) {
         Side u = user_side(src, far->bytes);
-        err = side_copy(*far, 0, nullptr, 0, u, 0, far->bytes, far->rec, nullptr, &used);
+        err = side_copy(*far, 0, nullptr, 0, u, 0, far->bytes, far, nullptr, &used);
     } else {
         uint64_t n = std::min(dst->local.bytes, far->bytes);
         Side u = user_side(src, n);
         // window first, then window -> far side (the user pointer may be pageable host memory)
         err = side_copy(dst->local, 0, nullptr, 0, u, 0, n, nullptr, nullptr, &used);
-        if (!err) err = side_copy(*far, 0, nullptr, 0, dst->local, 0, n, far->rec, nullptr, &used);
+        if (!err) err = side_copy(*far, 0, nullptr, 0, dst->local, 0, n, far, nullptr, &used);
     }
     return finish_sync(err, used, nullptr);
 }

@@ -55,7 +55,14 @@ struct Side {
     uint64_t    offset = 0;
     uint64_t    bytes = 0;            // usable (requested) bytes
     void       *ptr = nullptr;
-    Region     *rec = nullptr;        // table record (signal word lives here)
+    Region     *rec = nullptr;        // table record
+    TableHeader *hdr = nullptr;       // the table that holds rec (for the signal total)
+    // The completion counters THIS handle adds to.  One writing agent per word (tables.hpp, SigExt): the
+    // owner's handle uses Region::signal / signal_cpu, an attached handle the slot of its rank's GPU / the
+    // CPU slot of the block's extension record.
+    std::atomic<uint64_t> *sig_gpu = nullptr;
+    std::atomic<uint64_t> *sig_cpu = nullptr;
+    uint64_t *gpu_signal() const { return reinterpret_cast<uint64_t *>(sig_gpu); }
     bool valid() const { return backing != SIDE_NONE; }
 };
 
@@ -131,7 +138,7 @@ unsigned *next_ticket();
 
 // copy engine (copy.cpp)
 int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2_off, const Side &src, uint64_t src_off,
-              uint64_t bytes, Region *signal_rec, void *stream, bool *used_stream);
+              uint64_t bytes, const Side *sig, void *stream, bool *used_stream);
 struct DeviceGuard {
     int prev = -1;
     bool switched = false;

@@ -162,7 +162,7 @@ int ocmk_sort_u64(uint64_t *keys, uint64_t *tmp, uint64_t n, void *stream) {
 }
 
 // ---- strided copies on allocations -------------------------------------------------
-static int strided_sides(const Side &dst, const Side &src, const struct ocm_strided *d, Region *sig, void *stream) {
+static int strided_sides(const Side &dst, const Side &src, const struct ocm_strided *d, const Side *sig, void *stream) {
     Ctx &c = ctx();
     if (c.device < 0) return OCM_ENOGPU;
     if (!dst.ptr || !src.ptr) return OCM_EINVAL;
@@ -208,7 +208,7 @@ static int strided_sides(const Side &dst, const Side &src, const struct ocm_stri
     cudaStream_t st = (cudaStream_t)(stream ? stream : c.stream);
     c.n_copies.fetch_add(1, std::memory_order_relaxed);
     c.copy_bytes.fetch_add(d->extent[0] * n[0] * n[1] * n[2], std::memory_order_relaxed);
-    cudaError_t e = ocmk::launch_strided(k, sig ? reinterpret_cast<uint64_t *>(&sig->signal) : nullptr, next_ticket(), st,
+    cudaError_t e = ocmk::launch_strided(k, sig ? sig->gpu_signal() : nullptr, next_ticket(), st,
                                          &c.kernel_launches);
     if (e == cudaSuccess) return OCM_OK;
     LOGE("strided kernel: %s", cudaGetErrorString(e));
@@ -224,7 +224,7 @@ int ocm_copy_strided(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_strided 
     // the far side is the target when there is one, like a one-hop ocm_copy
     const Side &D = (dst->paired && dst->remote.valid()) ? dst->remote : dst->local;
     const Side &S = (src->paired && src->remote.valid()) ? src->remote : src->local;
-    int err = strided_sides(D, S, d, D.rec, stream);
+    int err = strided_sides(D, S, d, &D, stream);
     if (!err && !stream) {
         dst->lib_stream_pending.store(true);
         src->lib_stream_pending.store(true);
@@ -235,7 +235,7 @@ int ocm_copy_strided(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_strided 
 
 int ocm_copy_onesided_strided(ocm_alloc_t a, const struct ocm_strided *d, void *stream) {
     if (!a || !d || a->magic != kAllocMagic || !a->paired || !a->remote.valid() || !a->local.valid()) return -OCM_EINVAL;
-    int err = d->op_flag ? strided_sides(a->remote, a->local, d, a->remote.rec, stream)
+    int err = d->op_flag ? strided_sides(a->remote, a->local, d, &a->remote, stream)
                          : strided_sides(a->local, a->remote, d, nullptr, stream);
     if (!err && !stream) a->lib_stream_pending.store(true);
     set_last_error(err);

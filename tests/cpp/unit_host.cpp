@@ -190,6 +190,26 @@ static void t_tables() {
     BlockRef hb;
     CHECK(pool_alloc(h, TIER_HOST, 5000, 1, 0, &hb) == OCM_OK && hb.block_bytes == 8192);
     CHECK(pool_alloc(h, 7, 1, 1, 0, &hb) == OCM_EINVAL);
+    // per-writer completion counters of a shared block: claimed once, summed, released with the block
+    Region &hr = table_regions(h, TIER_HOST)[hb.region];
+    CHECK(hr.ext.load() == 0 && region_signal_total(h, hr) == 0);
+    SigExt *x = sigext_claim(h, TIER_HOST, hb.region);
+    CHECK(x != nullptr && hr.ext.load() != 0 && x->id == hb.id);
+    CHECK(sigext_claim(h, TIER_HOST, hb.region) == x);                     // idempotent
+    hr.signal.fetch_add(2);
+    hr.signal_cpu.fetch_add(3);
+    x->slot[1].fetch_add(5);
+    x->slot[kSigCpuSlot].fetch_add(7);
+    CHECK(region_signal_total(h, hr) == 17);
+    BlockRef hb2;
+    CHECK(pool_alloc(h, TIER_HOST, 100, 1, 0, &hb2) == OCM_OK);
+    SigExt *y = sigext_claim(h, TIER_HOST, hb2.region);
+    CHECK(y != nullptr && y != x);
+    CHECK(pool_free(h, TIER_HOST, hb.region, hb.id) == OCM_OK);
+    CHECK(x->owner.load() == 0 && hr.ext.load() == 0 && y->owner.load() != 0);   // record is free again
+    BlockRef hb3;
+    CHECK(pool_alloc(h, TIER_HOST, 100, 1, 0, &hb3) == OCM_OK);
+    CHECK(sigext_claim(h, TIER_HOST, hb3.region) == x && x->slot[1].load() == 0);   // reused, counters cleared
 }
 
 static void t_tables_mt() {
