@@ -150,11 +150,14 @@ int ocm_copy_onesided_async(ocm_alloc_t a, const struct ocm_params *p, void *str
 /* Wait for everything enqueued on the library's own copy stream. */
 int ocm_quiet(void);
 
-/* Completion signal of an allocation: a 64-bit counter in device-visible
+/* Completion signal of an allocation: a 64-bit count kept in device-visible
  * pinned memory next to the allocation's table entry.  Every put that names
  * the allocation as destination adds 1 to it with release semantics at system
  * scope after its last byte is visible (replaces ib_poll / rma2 notifications,
- * reference src/rdma.c:267-302, src/extoll.c:145-166). */
+ * reference src/rdma.c:267-302, src/extoll.c:145-166).  Internally the count is
+ * the sum of several words with one writing agent each (the owner's GPU, CPUs,
+ * and for shared blocks one word per rank's GPU): GPUs cannot add atomically to
+ * the same host word on boxes without PCIe atomics. */
 int ocm_signal_read(ocm_alloc_t a, uint64_t *value);
 int ocm_signal_wait(ocm_alloc_t a, uint64_t at_least, int timeout_ms);
 
