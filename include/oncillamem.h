@@ -140,6 +140,13 @@ uint64_t ocm_slab_bytes(ocm_alloc_t a);
  * allocations made after that are multicast-backed (one multimem.st stream reaches every GPU). */
 int      ocm_multicast_ready(void);
 int      ocm_is_multicast(ocm_alloc_t a);
+/* NVLS gather-reduce on a multicast-backed OCM_REPLICATED_GPU allocation:
+ *   window[src_offset .. +bytes) = element-wise fp32 SUM over every rank's replica of far[dest_offset .. +bytes)
+ * in one multimem.ld_reduce stream (the NVSwitch adds the replicas; the "get" counterpart of the multicast
+ * put and the reduce half of an in-switch all-reduce).  Each rank writes its own contribution into its replica
+ * (ocm_slab_ptr(a, ocm_rank())); ordering those writes before the reduce is the caller's business.  Offsets
+ * and bytes are multiples of 16.  -OCM_EUNSUPPORTED when the allocation is not multicast-backed. */
+int      ocm_reduce_get_f32(ocm_alloc_t a, const struct ocm_params *p, void *stream);
 
 /* ---- stream-ordered copies ------------------------------------------ */
 /* `stream` is a cudaStream_t (NULL = the library's own copy stream).  The

@@ -150,6 +150,7 @@ _sig("ocm_copy_onesided_async", C.c_int, ocm_alloc_t, P(ocm_params), C.c_void_p)
 _sig("ocm_quiet", C.c_int)
 _sig("ocm_signal_read", C.c_int, ocm_alloc_t, P(C.c_uint64))
 _sig("ocm_signal_wait", C.c_int, ocm_alloc_t, C.c_uint64, C.c_int)
+_sig("ocm_reduce_get_f32", C.c_int, ocm_alloc_t, P(ocm_params), C.c_void_p)
 _sig("ocm_share", C.c_int, ocm_alloc_t, P(ocm_share_token))
 _sig("ocm_attach", C.c_int, P(ocm_share_token), P(ocm_alloc_t))
 _sig("ocm_attach_count", C.c_int, ocm_alloc_t)

@@ -232,6 +232,18 @@ class Allocation:
         """One-sided read far side[dest_offset] -> window[src_offset]."""
         _onesided(self, 0, nbytes, src_offset, dest_offset, stream)
 
+    def reduce_get_f32(self, nbytes: int | None = None, *, src_offset: int = 0, dest_offset: int = 0, stream=None) -> None:
+        """NVLS gather-reduce: window[src_offset:] = fp32 sum over every rank's replica of far[dest_offset:].
+
+        Multicast-backed ``OCM_REPLICATED_GPU`` allocations only; stream-ordered (``None`` = library stream,
+        wait with :func:`quiet`)."""
+        p = N.ocm_params()
+        p.src_offset, p.dest_offset = int(src_offset), int(dest_offset)
+        p.bytes = int(self.local_bytes if nbytes is None else nbytes)
+        r = lib.ocm_reduce_get_f32(self.handle, C.byref(p), C.c_void_p(_stream_ptr(stream)))
+        if r:
+            raise OcmError("ocm_reduce_get_f32", r)
+
     def copy_in(self, src_ptr: int) -> None:
         if lib.ocm_copy_in(self.handle, C.c_void_p(src_ptr)) != 0:
             raise OcmError("ocm_copy_in")

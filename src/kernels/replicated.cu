@@ -181,6 +181,31 @@ cudaError_t launch_put_replicated(void *const *dsts, int n_dst, const void *src,
     return cudaLaunchKernelEx(&cfg, ocm_put_replicated_kernel, a);
 }
 
+// (c) NVLS gather-reduce: dst[i] = sum over all GPUs bound to the multicast object of their replica's
+// element i (fp32).  One multimem.ld_reduce per 16 bytes: the NVSwitch fetches and adds the replicas, the
+// reading GPU receives one result - the "get" counterpart of the multimem.st put, and the first half of an
+// in-switch all-reduce.  Two loads in flight per thread.
+__global__ void __launch_bounds__(256) ocm_get_reduce_f32_kernel(float4 *dst, const uint8_t *mc_src, uint64_t n16) {
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + stride < n16; i += 2 * stride) {
+        const float4 a = multimem_ld_reduce_add_f32x4(mc_src + i * 16);
+        const float4 b = multimem_ld_reduce_add_f32x4(mc_src + (i + stride) * 16);
+        dst[i] = a;
+        dst[i + stride] = b;
+    }
+    if (i < n16) dst[i] = multimem_ld_reduce_add_f32x4(mc_src + i * 16);
+}
+
+cudaError_t launch_get_reduce_f32(void *dst, const void *mc_src, size_t bytes, cudaStream_t stream) {
+    if (((uintptr_t)dst | (uintptr_t)mc_src | bytes) & 15) return cudaErrorMisalignedAddress;
+    if (!bytes) return cudaSuccess;
+    int ctas = (int)std::min<uint64_t>(std::max<uint64_t>((bytes / 16 + 511) / 512, 1), (uint64_t)num_sms() * 4);
+    ocm_get_reduce_f32_kernel<<<ctas, 256, 0, stream>>>(static_cast<float4 *>(dst), static_cast<const uint8_t *>(mc_src),
+                                                       bytes / 16);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_put_multimem(void *mc_dst, const void *src, size_t bytes, uint64_t *mc_signal, unsigned *ticket,
                                 cudaStream_t stream) {
     if (((uintptr_t)mc_dst | (uintptr_t)src | bytes) & 15) return cudaErrorMisalignedAddress;

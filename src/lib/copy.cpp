@@ -522,6 +522,34 @@ int ocm_copy_onesided(ocm_alloc_t a, ocm_param_t p) {
     return finish_sync(err, used, nullptr);
 }
 
+// NVLS gather-reduce (K6, multimem.ld_reduce): window = sum over all ranks' replicas.  Stream-ordered like the
+// *_async calls (stream NULL = the library's copy stream; ocm_quiet / ocm_free wait for it).
+int ocm_reduce_get_f32(ocm_alloc_t a, const struct ocm_params *p, void *stream) {
+    TraceRange tr_("ocm_reduce_get_f32");
+    Ctx &c = ctx();
+    int err = OCM_OK;
+    if (!valid(a) || !p) err = OCM_EINVAL;
+    else if (a->kind != OCM_REPLICATED_GPU || !a->mc || !a->mc_ptr || c.device < 0) err = OCM_EUNSUPPORTED;
+    else if (!a->local.valid() || a->local.tier != TIER_GPU) err = OCM_EINVAL;
+    else if (!fits(a->local, p->src_offset, p->bytes) || p->bytes > a->stripe_bytes ||
+             p->dest_offset > a->stripe_bytes - p->bytes)
+        err = OCM_ERANGE;
+    else if ((p->src_offset | p->dest_offset | p->bytes) & 15) err = OCM_EINVAL;
+    if (!err && p->bytes) {
+        DeviceGuard dg(c.device);
+        err = cuda_err(ocmk::launch_get_reduce_f32((char *)a->local.ptr + p->src_offset, (const char *)a->mc_ptr + p->dest_offset,
+                                                   p->bytes, (cudaStream_t)(stream ? stream : c.stream)),
+                       "multimem reduce");
+        ++c.kernel_launches;
+        note_other_gpu_op();
+        c.n_copies.fetch_add(1, std::memory_order_relaxed);
+        c.copy_bytes.fetch_add(p->bytes * a->stripes.size(), std::memory_order_relaxed);
+        mark_pending(a, stream, true);
+    }
+    set_last_error(err);
+    return -err;
+}
+
 int ocm_quiet(void) {
     Ctx &c = ctx();
     if (c.device < 0 || !c.stream) return 0;

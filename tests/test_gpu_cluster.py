@@ -263,6 +263,47 @@ def test_nvls_multicast_replicated_put(gpu_cluster):
     b.free()
 
 
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="NVLS multicast needs two GPUs")
+def test_nvls_gather_reduce(gpu_cluster):
+    """multimem.ld_reduce: the window receives the fp32 sum of every rank's replica, added inside the NVSwitch."""
+    from oncilla_b200 import api
+
+    if not api.multicast_ready(wait_s=10.0):
+        pytest.skip("NVLS multicast not available on this box")
+    N = ocm.num_ranks()
+    elems = (3 << 18) + 4                                    # 3 MiB + 16 bytes of fp32
+    nbytes = elems * 4
+    a = ocm.alloc(ocm.OCM_REPLICATED_GPU, nbytes, nbytes)
+    assert a.is_multicast
+    g = torch.Generator(device="cuda").manual_seed(5)
+    parts = [torch.randn(elems, device="cuda", generator=g) for _ in range(N)]
+    for r in range(N):                                       # every replica gets a different contribution
+        a.slab_tensor(r, torch.float32)[:elems].copy_(parts[r])
+    torch.cuda.synchronize()
+    a.local_tensor(torch.float32).fill_(-1.0)
+    before = ops.launch_count()
+    a.reduce_get_f32(nbytes, stream=torch.cuda.current_stream())
+    torch.cuda.synchronize()
+    assert ops.launch_count() == before + 1
+    want = torch.stack(parts).sum(0)
+    got = a.local_tensor(torch.float32)[:elems]
+    assert torch.allclose(got, want, rtol=1e-6, atol=1e-6)
+    # a sub-range at offsets
+    a.local_tensor(torch.float32).fill_(-1.0)
+    a.reduce_get_f32(4096, src_offset=1024, dest_offset=8192, stream=torch.cuda.current_stream())
+    torch.cuda.synchronize()
+    got = a.local_tensor(torch.float32)
+    assert torch.allclose(got[256 : 256 + 1024], want[2048 : 2048 + 1024], rtol=1e-6, atol=1e-6)
+    assert float(got[255]) == -1.0 and float(got[256 + 1024]) == -1.0
+    with pytest.raises(ocm.OcmError):
+        a.reduce_get_f32(4096, src_offset=8)                 # misaligned
+    plain = ocm.alloc(ocm.OCM_REMOTE_GPU, 4096, 4096)
+    with pytest.raises(ocm.OcmError):
+        plain.reduce_get_f32(4096)                           # not a multicast allocation
+    plain.free()
+    a.free()
+
+
 ATTACH_PEER = r"""
 import sys, torch
 import oncilla_b200 as ocm
