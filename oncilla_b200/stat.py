@@ -1,0 +1,57 @@
+"""``python -m oncilla_b200.stat`` - one line per rank of a running cluster: pool sizes, usage, live blocks.
+
+Attaches like any application (``OCM_RANK`` / ``OCM_NS`` select the cluster), asks every
+daemon for its counters (``ocm_get_rank_stats`` -> ``MSG_STATS``, forwarded by the local daemon) and leaves.
+The reference has no observability beyond ``OCM_VERBOSE`` printf lines.
+"""
+from __future__ import annotations
+
+import json
+import sys
+
+from . import api
+
+
+def _fmt(n: int) -> str:
+    for unit, div in (("GiB", 1 << 30), ("MiB", 1 << 20), ("KiB", 1 << 10)):
+        if n >= div:
+            return f"{n / div:.1f} {unit}"
+    return f"{n} B"
+
+
+def collect() -> list[dict]:
+    rows = []
+    for r in range(api.num_ranks()):
+        try:
+            s = api.stats(r)
+            s["rank"] = r
+            s["reachable"] = True
+        except Exception as e:  # a dead daemon must not hide the others
+            s = {"rank": r, "reachable": False, "error": str(e)}
+        rows.append(s)
+    return rows
+
+
+def main(argv=None) -> int:
+    argv = sys.argv[1:] if argv is None else argv
+    api.init()
+    try:
+        rows = collect()
+    finally:
+        api.tini()
+    if "--json" in argv:
+        print(json.dumps(rows))
+        return 0
+    print(f"{'rank':>4}  {'HBM pool':>10} {'used':>10}  {'host pool':>10} {'used':>10}  {'live':>6} {'allocs':>8} {'frees':>8}")
+    for s in rows:
+        if not s["reachable"]:
+            print(f"{s['rank']:>4}  unreachable: {s['error']}")
+            continue
+        print(f"{s['rank']:>4}  {_fmt(s['pool_gpu_bytes']):>10} {_fmt(s['pool_gpu_used']):>10}  "
+              f"{_fmt(s['pool_host_bytes']):>10} {_fmt(s['pool_host_used']):>10}  "
+              f"{s['allocs_live']:>6} {s['allocs_total']:>8} {s['frees_total']:>8}")
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

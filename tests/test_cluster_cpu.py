@@ -32,6 +32,28 @@ def test_ocm_test_program(cluster2, path, test, args):
     assert "FAIL" not in out
 
 
+def test_example_hello_ocm(cluster2):
+    """examples/hello_ocm.c: public header + libocm only, the reference's call sequence."""
+    out = _ok(run_app(cluster2, 0, [BIN / "hello_ocm"]))
+    assert "pass: hello_ocm" in out and "far side 1048576 bytes on rank 1" in out
+    out = _ok(run_app(cluster2, 1, [BIN / "hello_ocm", "3"]))          # the reference's OCM_REMOTE_RDMA kind
+    assert "pass: hello_ocm" in out and "on rank 0" in out
+
+
+def test_stat_tool(cluster2):
+    """python -m oncilla_b200.stat: per-rank pool counters through MSG_STATS."""
+    env = cluster2.env(0)
+    env["PYTHONPATH"] = str(REPO) + os.pathsep + env.get("PYTHONPATH", "")
+    r = subprocess.run([sys.executable, "-m", "oncilla_b200.stat", "--json"], env=env, capture_output=True, text=True,
+                       timeout=60)
+    assert r.returncode == 0, r.stderr
+    rows = json.loads(r.stdout.strip().splitlines()[-1])
+    assert [x["rank"] for x in rows] == [0, 1] and all(x["reachable"] for x in rows)
+    assert all(x["pool_host_bytes"] == 32 << 20 for x in rows)
+    r = subprocess.run([sys.executable, "-m", "oncilla_b200.stat"], env=env, capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0 and "host pool" in r.stdout and "32.0 MiB" in r.stdout
+
+
 API_SNIPPET = r"""
 import json, torch, ctypes
 import oncilla_b200 as ocm

@@ -348,6 +348,15 @@ def test_native_ocm_test_program_gpu(gpu_cluster):
         assert "pass: OCM test completed successfully" in r.stdout
 
 
+def test_examples_on_gpu(gpu_cluster):
+    """examples/: the C hello program with a remote-GPU pair, and a user kernel that works on the far side
+    through ocm_remote_ptr()."""
+    r = run_app(gpu_cluster, 0, [BIN / "hello_ocm", "7"])
+    assert r.returncode == 0 and "pass: hello_ocm" in r.stdout, r.stdout + r.stderr
+    r = run_app(gpu_cluster, 0, [BIN / "peer_kernel"])
+    assert r.returncode == 0 and "pass: peer_kernel" in r.stdout, r.stdout + r.stderr
+
+
 def test_workloads_gups_and_sort(gpu_cluster):
     from oncilla_b200.models import gups, sort
 
