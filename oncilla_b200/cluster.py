@@ -210,6 +210,16 @@ class LocalCluster:
             p.send_signal(sig)
             p.wait(timeout=10)
 
+    def restart(self, rank: int, timeout: float = 60.0) -> None:
+        """Kill ``rank``'s daemon (if it still runs) and start a fresh one on the same nodefile line."""
+        self.kill(rank)
+        log = self.logs[rank] + ".restart"
+        self.logs[rank] = log
+        with open(log, "w") as f:
+            self.procs[rank] = subprocess.Popen([str(_native.DAEMON_PATH), self.nodefile], env=self.env(rank), stdout=f,
+                                                stderr=subprocess.STDOUT, start_new_session=True)
+        self._wait_ready(rank, timeout)
+
     def stop(self) -> None:
         for r, p in self.procs.items():
             if p.poll() is None:

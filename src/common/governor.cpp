@@ -3,6 +3,7 @@
 #include "../../include/oncillamem.h"
 #include <algorithm>
 #include <cstring>
+#include <ctime>
 
 namespace ocm {
 
@@ -27,6 +28,7 @@ int governor_add_node(ClusterTable *c, int rank, const NodeConfig &cfg, const ui
         for (int t = 0; t < TIER_COUNT; ++t) n.used[t].store(0, std::memory_order_relaxed);
         n.live.store(0, std::memory_order_relaxed);
     }
+    n.heartbeat_ns.store(0, std::memory_order_relaxed);   // alive until the first beat says otherwise
     n.joined.store(1, std::memory_order_release);
     LOGI("rank %d %s: gpu=%d pool gpu=%llu host=%llu", rank, rejoin ? "re-joined" : "joined", cfg.gpu_index,
          (unsigned long long)pool_bytes[TIER_GPU], (unsigned long long)pool_bytes[TIER_HOST]);
@@ -35,9 +37,27 @@ int governor_add_node(ClusterTable *c, int rank, const NodeConfig &cfg, const ui
 
 void governor_release(ClusterTable *c, int rank, int tier, uint64_t bytes) { cluster_unreserve(c, rank, tier, bytes); }
 
-static bool try_rank(ClusterTable *c, int rank, Tier want, uint64_t bytes, Tier *got) {
+static uint64_t mono_now_ns() {
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (uint64_t)ts.tv_sec * 1000000000ull + (uint64_t)ts.tv_nsec;
+}
+
+bool governor_rank_alive(const ClusterTable *c, int rank) {
+    if (rank < 0 || rank >= c->n_ranks || !c->node[rank].joined.load(std::memory_order_acquire)) return false;
+    const uint64_t beat = c->node[rank].heartbeat_ns.load(std::memory_order_relaxed);
+    if (!beat) return true;
+    const uint64_t now = mono_now_ns();
+    return now < beat || now - beat < kRankDeadAfterNs;
+}
+
+static bool try_rank(ClusterTable *c, int rank, Tier want, uint64_t bytes, Tier *got, bool *dead) {
     if (rank < 0 || rank >= c->n_ranks) return false;
     if (!c->node[rank].joined.load(std::memory_order_acquire)) return false;
+    if (!governor_rank_alive(c, rank)) {   // its daemon stopped beating: place elsewhere (the reference hangs here)
+        *dead = true;
+        return false;
+    }
     if (c->node[rank].pool_bytes[want] && cluster_reserve(c, rank, want, bytes)) {
         *got = want;
         return true;
@@ -97,9 +117,10 @@ int governor_place(ClusterTable *c, const AllocRequest &req, Allocation *out) {
         return OCM_EINVAL;
     }
 
+    bool dead = false;
     for (int i = 0; i < n; ++i) {
         Tier got;
-        if (!try_rank(c, order[i], want, req.bytes, &got)) continue;
+        if (!try_rank(c, order[i], want, req.bytes, &got, &dead)) continue;
         memset(out, 0, sizeof *out);
         out->orig_rank = req.orig_rank;
         out->remote_rank = order[i];
@@ -114,7 +135,7 @@ int governor_place(ClusterTable *c, const AllocRequest &req, Allocation *out) {
         }
         return OCM_OK;
     }
-    return OCM_ENOMEM;
+    return dead ? OCM_ENODAEMON : OCM_ENOMEM;   // nobody had room - or the only candidates are gone
 }
 
 } // namespace ocm

@@ -37,4 +37,10 @@ int governor_add_node(ClusterTable *c, int rank, const NodeConfig &cfg, const ui
 
 int governor_joined(const ClusterTable *c);
 
+// True while the rank's daemon keeps its heartbeat in the cluster table fresh (NodeSlot::heartbeat_ns).
+// governor_place skips ranks that are not: allocations move on to the next candidate of the policy, and
+// return OCM_ENODAEMON instead of OCM_ENOMEM when dead ranks were the only candidates.  The reference has no
+// failure detection at all: a request for a dead node blocks in connect() or forever.
+bool governor_rank_alive(const ClusterTable *c, int rank);
+
 } // namespace ocm

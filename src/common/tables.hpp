@@ -127,7 +127,11 @@ struct NodeSlot {
     std::atomic<uint64_t> live;
     uint64_t gpu_mem[kMaxGpus];
     char     ip[64];
+    // Liveness: the rank's daemon stores CLOCK_MONOTONIC here on every timer tick (20 ms).  0 = has not
+    // beaten yet (just joined, or a table without daemons in the unit tests) and counts as alive.
+    std::atomic<uint64_t> heartbeat_ns;
 };
+constexpr uint64_t kRankDeadAfterNs = 1500ull * 1000000ull;
 
 struct ClusterTable {
     uint64_t magic;

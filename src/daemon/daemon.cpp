@@ -909,6 +909,9 @@ void Daemon::on_timer() {
     }
     uint64_t now = now_ns();
     tbl_->heartbeat_ns.store(now, std::memory_order_relaxed);
+    if (joined_) {   // the placement code of every process reads this one (governor_rank_alive)
+        if (ClusterTable *ct = shared_cluster()) ct->node[rank_].heartbeat_ns.store(now, std::memory_order_relaxed);
+    }
     if (!joined_) {
         bool waiting = false;
         for (auto &kv : pending_) waiting |= kv.second.stage == ST_WAIT_JOIN;

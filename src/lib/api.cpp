@@ -237,6 +237,13 @@ static int alloc_side(uint32_t type, uint64_t bytes, int policy, int explicit_ra
             int err = governor_place(c.cluster, req, &a);
             if (err) return err;
             RankView *v = get_view(a.remote_rank, a.tier == TIER_GPU);
+            if (v && v->hdr->daemon_pid != c.cluster->node[a.remote_rank].daemon_pid) {
+                // that rank's daemon was restarted after we mapped its tables: our view is of the old, orphaned
+                // segment.  Re-attach (ocm_tini + ocm_init) to see the new one.
+                LOGW("rank %d was restarted (daemon pid %d -> %d); ocm_tini/ocm_init re-attaches", a.remote_rank,
+                     v->hdr->daemon_pid, c.cluster->node[a.remote_rank].daemon_pid);
+                v = nullptr;
+            }
             err = v ? pool_alloc(v->hdr, (int)a.tier, bytes, (int)getpid(), c.rank, &b) : OCM_ENODAEMON;
             if (!err) break;
             governor_release(c.cluster, a.remote_rank, (int)a.tier, bytes);

@@ -316,6 +316,53 @@ print("RESULT " + json.dumps({"ranks": ranks, "ok": ok, "used": used, "after": a
         assert res["after"] == [0, 0, 0]
 
 
+PLACE_SNIPPET = r"""
+import json, oncilla_b200 as ocm
+ocm.init()
+res = {}
+for path, flags in (("fast", 0), ("daemon", ocm.ALLOC_SLOW_PATH)):
+    try:
+        a = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 1 << 20, flags=flags)
+        a.local_tensor()[:] = 5; a.put(); a.local_tensor()[:] = 0; a.get()
+        res[path] = [a.remote_rank, int(a.local_tensor().sum()) == 5 * 4096]
+        a.free()
+    except ocm.OcmError as e:
+        res[path] = ["error", e.err]
+    try:
+        b = ocm.alloc(ocm.OCM_REMOTE_HOST, 0, 4096, policy=ocm.POLICY_EXPLICIT, rank=1, flags=flags | ocm.ALLOC_NO_WINDOW)
+        res[path + "_explicit1"] = b.remote_rank
+        b.free()
+    except ocm.OcmError as e:
+        res[path + "_explicit1"] = ["error", e.err]
+ocm.tini()
+print("RESULT " + json.dumps(res))
+"""
+
+
+def test_dead_rank_is_skipped_and_rejoins():
+    """Elastic placement: when a rank's daemon dies, its heartbeat in the cluster table goes stale and both
+    allocation paths move on to the next neighbour (explicit requests for it fail with OCM_ENODAEMON instead
+    of hanging like the reference); a restarted daemon re-joins and is used again."""
+    with ocm.LocalCluster(3, host_bytes=16 << 20, extra_env={"OCM_NO_GPU": "1"}) as cl:
+        def place():
+            out = _ok(run_py(cl, 0, PLACE_SNIPPET))
+            return json.loads(out.split("RESULT ", 1)[1])
+
+        res = place()
+        assert res["fast"] == [1, True] and res["daemon"] == [1, True]
+        assert res["fast_explicit1"] == 1 and res["daemon_explicit1"] == 1
+        cl.kill(1)
+        time.sleep(2.0)                                  # heartbeat timeout is 1.5 s
+        res = place()
+        assert res["fast"] == [2, True] and res["daemon"] == [2, True], res
+        assert res["fast_explicit1"] == ["error", 3] and res["daemon_explicit1"] == ["error", 3], res   # OCM_ENODAEMON
+        cl.restart(1)
+        time.sleep(0.3)
+        res = place()
+        assert res["fast"] == [1, True] and res["daemon"] == [1, True], res
+        assert res["fast_explicit1"] == 1 and res["daemon_explicit1"] == 1
+
+
 def test_app_death_is_reclaimed(cluster2):
     """A crashed application's regions return to the pool (TODO in reference README:68-69)."""
     code = r"""
