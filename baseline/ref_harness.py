@@ -55,6 +55,9 @@ def main(args) -> None:
                            "reference is impossible: it has neither setup.py nor pyproject.toml")
     if shutil.which("unshare") is None:
         return unavailable("unshare(1) missing: cannot give each reference daemon its own hostname/IPC namespace")
+    if not os.path.exists("/dev/nvidiactl"):
+        return unavailable("no CUDA device on this machine: the reference ignores every cudaMalloc/cudaMemcpy error "
+                           "except out-of-memory (src/lib.c:240-249,640), so its GPU copy would 'run' and time nothing")
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", str(rank)))
     world = int(os.environ.get("WORLD_SIZE", "1"))
