@@ -18,6 +18,10 @@ int governor_add_node(ClusterTable *c, int rank, const NodeConfig &cfg, const ui
     if (rank < 0 || rank >= c->n_ranks || rank >= kMaxRanks) return OCM_EINVAL;
     NodeSlot &n = c->node[rank];
     bool rejoin = n.joined.load(std::memory_order_acquire) != 0;
+    // The same daemon asking again keeps its accounting; a NEW daemon process on that rank (restart after a
+    // crash) comes with empty pools, so what the old incarnation had handed out no longer counts.
+    const bool new_incarnation = rejoin && n.daemon_pid != cfg.daemon_pid;
+    if (new_incarnation) rejoin = false;
     n.daemon_pid = cfg.daemon_pid;
     n.gpu_index = cfg.gpu_index;
     n.num_gpu = cfg.num_gpu;
@@ -30,7 +34,8 @@ int governor_add_node(ClusterTable *c, int rank, const NodeConfig &cfg, const ui
     }
     n.heartbeat_ns.store(0, std::memory_order_relaxed);   // alive until the first beat says otherwise
     n.joined.store(1, std::memory_order_release);
-    LOGI("rank %d %s: gpu=%d pool gpu=%llu host=%llu", rank, rejoin ? "re-joined" : "joined", cfg.gpu_index,
+    LOGI("rank %d %s: gpu=%d pool gpu=%llu host=%llu", rank,
+         new_incarnation ? "re-joined after a restart" : rejoin ? "re-joined" : "joined", cfg.gpu_index,
          (unsigned long long)pool_bytes[TIER_GPU], (unsigned long long)pool_bytes[TIER_HOST]);
     return OCM_OK;
 }

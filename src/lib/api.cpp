@@ -150,6 +150,16 @@ RankView *get_view(int rank, bool with_gpu) {
     if (rank < 0 || rank >= kMaxRanks) return nullptr;
     RankView *v = &c.view[rank];
     std::lock_guard<std::mutex> g(c.mu);
+    if (v->ok && c.cluster && rank < c.n_ranks && rank != c.rank &&
+        c.cluster->node[rank].joined.load(std::memory_order_acquire) &&
+        c.cluster->node[rank].daemon_pid != v->hdr->daemon_pid) {
+        // That rank's daemon was restarted: it formatted new tables and a new pool under the same names.  Keep
+        // the old mappings for the handles that still point into them, and map the new incarnation.
+        LOGW("rank %d was restarted (daemon pid %d -> %d): mapping its new tables", rank, v->hdr->daemon_pid,
+             c.cluster->node[rank].daemon_pid);
+        c.orphaned.push_back(*v);
+        *v = RankView();
+    }
     if (!v->tried) {
         v->tried = true;
         std::string err;
@@ -185,21 +195,24 @@ RankView *get_view(int rank, bool with_gpu) {
     return v;
 }
 
+static void drop_view(RankView &v) {
+    if (v.gpu.ptr) gpu::pool_release(&v.gpu);
+    if (v.host_map.base) {
+        gpu::host_unregister(v.host_map.base);
+        shm_close(&v.host_map, false);
+    }
+    if (v.tbl_map.base) {
+        gpu::host_unregister(v.tbl_map.base);
+        shm_close(&v.tbl_map, false);
+    }
+    v = RankView();
+}
+
 static void drop_views() {
     Ctx &c = ctx();
-    for (int r = 0; r < kMaxRanks; ++r) {
-        RankView &v = c.view[r];
-        if (v.gpu.ptr) gpu::pool_release(&v.gpu);
-        if (v.host_map.base) {
-            gpu::host_unregister(v.host_map.base);
-            shm_close(&v.host_map, false);
-        }
-        if (v.tbl_map.base) {
-            gpu::host_unregister(v.tbl_map.base);
-            shm_close(&v.tbl_map, false);
-        }
-        v = RankView();
-    }
+    for (int r = 0; r < kMaxRanks; ++r) drop_view(c.view[r]);
+    for (auto &v : c.orphaned) drop_view(v);
+    c.orphaned.clear();
 }
 
 // ------------------------------------------------------------ side helpers --
@@ -237,13 +250,6 @@ static int alloc_side(uint32_t type, uint64_t bytes, int policy, int explicit_ra
             int err = governor_place(c.cluster, req, &a);
             if (err) return err;
             RankView *v = get_view(a.remote_rank, a.tier == TIER_GPU);
-            if (v && v->hdr->daemon_pid != c.cluster->node[a.remote_rank].daemon_pid) {
-                // that rank's daemon was restarted after we mapped its tables: our view is of the old, orphaned
-                // segment.  Re-attach (ocm_tini + ocm_init) to see the new one.
-                LOGW("rank %d was restarted (daemon pid %d -> %d); ocm_tini/ocm_init re-attaches", a.remote_rank,
-                     v->hdr->daemon_pid, c.cluster->node[a.remote_rank].daemon_pid);
-                v = nullptr;
-            }
             err = v ? pool_alloc(v->hdr, (int)a.tier, bytes, (int)getpid(), c.rank, &b) : OCM_ENODAEMON;
             if (!err) break;
             governor_release(c.cluster, a.remote_rank, (int)a.tier, bytes);
@@ -301,10 +307,15 @@ static int release_side(Side &s) {
     Ctx &c = ctx();
     int err = OCM_OK;
     switch (s.backing) {
-    case SIDE_POOL:
-        if (!s.via_daemon && c.cluster) {
-            RankView *v = get_view(s.rank, false);
-            err = v ? pool_free(v->hdr, s.tier, s.region, s.id) : OCM_ENODAEMON;
+    case SIDE_POOL: {
+        RankView *cur = get_view(s.rank, false);
+        if (s.hdr && (!cur || cur->hdr != s.hdr)) {
+            // the block lives in a pool whose daemon has been restarted since: the memory and its accounting went
+            // with the old incarnation; release it in the orphaned table only (ids restart, never touch the new one)
+            pool_free(s.hdr, s.tier, s.region, s.id);
+            err = OCM_ESTALE;
+        } else if (!s.via_daemon && c.cluster) {
+            err = cur ? pool_free(cur->hdr, s.tier, s.region, s.id) : OCM_ENODAEMON;
             if (!err) governor_release(c.cluster, s.rank, s.tier, s.bytes);
         } else {
             Message m;
@@ -318,6 +329,7 @@ static int release_side(Side &s) {
         }
         if (s.ptr) c.bytes_live[s.tier].fetch_sub(s.bytes, std::memory_order_relaxed);
         break;
+    }
     case SIDE_HEAP:
         if (c.device >= 0) gpu::host_unregister(s.ptr);
         free(s.ptr);

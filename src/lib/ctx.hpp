@@ -106,6 +106,9 @@ struct Ctx {
     ShmMapping   cluster_map;
     ClusterTable *cluster = nullptr;
     RankView     view[kMaxRanks];
+    // Views of ranks whose daemon has been restarted since: the mappings stay (handles made before the restart
+    // still point into them) but nothing new is placed there.  Released in ocm_tini.
+    std::vector<RankView> orphaned;
     std::unordered_set<lib_alloc *> allocs;
     void        *stream = nullptr;      // library copy stream
     unsigned    *tickets = nullptr;     // device-local election words

@@ -363,6 +363,63 @@ def test_dead_rank_is_skipped_and_rejoins():
         assert res["fast_explicit1"] == 1 and res["daemon_explicit1"] == 1
 
 
+SURVIVOR = r"""
+import json, os, time, oncilla_b200 as ocm
+d = os.environ["SYNC_DIR"]
+ocm.init()
+a = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 1 << 20)              # far side on rank 1, first incarnation
+a.local_tensor()[:] = 9; a.put()
+res = {"a_rank": a.remote_rank}
+open(d + "/allocated", "w").write("1")
+while not os.path.exists(d + "/restarted"): time.sleep(0.01)
+b = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 1 << 20)              # must land in the NEW pool of rank 1
+res["b_rank"] = b.remote_rank
+b.local_tensor()[:] = 4; b.put(); b.local_tensor()[:] = 0; b.get()
+res["b_ok"] = int(b.local_tensor().sum()) == 4 * 4096
+res["b_zero_tail"] = int(b.remote_tensor()[4096:].sum()) == 0   # fresh, zeroed memory (not a's 9s)
+try:
+    a.free(); res["a_free"] = "ok"
+except ocm.OcmError as e:
+    res["a_free"] = e.err
+res["used_mid"] = ocm.stats(rank=1)["pool_host_used"]
+b.free()
+time.sleep(0.2)
+res["live_end"] = ocm.stats(rank=1)["allocs_live"]
+ocm.tini()
+print("RESULT " + json.dumps(res))
+"""
+
+
+def test_application_survives_peer_daemon_restart(tmp_path):
+    """A long-lived application keeps working when the daemon of the rank that backs its memory is restarted:
+    new allocations land in the new incarnation's pool, handles from before the restart go stale instead of
+    corrupting the new tables, and the capacity accounting starts from zero."""
+    with ocm.LocalCluster(2, host_bytes=16 << 20, extra_env={"OCM_NO_GPU": "1"}) as cl:
+        env = cl.env(0)
+        env["PYTHONPATH"] = str(REPO) + os.pathsep + env.get("PYTHONPATH", "")
+        env["SYNC_DIR"] = str(tmp_path)
+        app = subprocess.Popen([sys.executable, "-c", SURVIVOR], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                               text=True)
+        try:
+            t0 = time.time()
+            while not (tmp_path / "allocated").exists():
+                assert app.poll() is None and time.time() - t0 < 60, app.stderr.read() if app.poll() is not None else "timeout"
+                time.sleep(0.02)
+            cl.restart(1)
+            time.sleep(0.3)
+            (tmp_path / "restarted").write_text("1")
+            out, err = app.communicate(timeout=60)
+        finally:
+            if app.poll() is None:
+                app.kill()
+        assert app.returncode == 0, err
+        res = json.loads(out.split("RESULT ", 1)[1])
+        assert res["a_rank"] == 1 and res["b_rank"] == 1 and res["b_ok"] and res["b_zero_tail"]
+        assert res["a_free"] == 8                                  # OCM_ESTALE: the block died with the old daemon
+        assert res["used_mid"] == 1 << 20                           # only b counts in the new incarnation
+        assert res["live_end"] == 0
+
+
 def test_app_death_is_reclaimed(cluster2):
     """A crashed application's regions return to the pool (TODO in reference README:68-69)."""
     code = r"""
