@@ -99,12 +99,17 @@ __device__ __forceinline__ uint64_t block_exclusive_scan_256(uint64_t v, uint64_
     return base + inc - v;
 }
 
+// zero_counts (may be null): the count matrix the FOLLOWING scatter kernel accumulates the next pass's histogram
+// into (fused mode, small inputs); row d is cleared by CTA d here, one launch ahead of its use.
 __global__ void __launch_bounds__(256) ocm_sort_scan_kernel(const uint32_t *counts, uint64_t *offsets, uint64_t *row_total,
-                                                            uint64_t *digit_base, int ctas, unsigned int *ticket) {
+                                                            uint64_t *digit_base, int ctas, unsigned int *ticket,
+                                                            uint32_t *zero_counts) {
     __shared__ uint64_t warp_sums[8];
     __shared__ bool last;
     const uint32_t *row = counts + (uint64_t)blockIdx.x * ctas;
     uint64_t *orow = offsets + (uint64_t)blockIdx.x * ctas;
+    if (zero_counts)
+        for (int i = threadIdx.x; i < ctas; i += 256) zero_counts[(uint64_t)blockIdx.x * ctas + i] = 0;
     uint64_t carry = 0;
     for (int base = 0; base < ctas; base += 256) {
         const int i = base + threadIdx.x;
@@ -124,6 +129,7 @@ __global__ void __launch_bounds__(256) ocm_sort_scan_kernel(const uint32_t *coun
     __threadfence();                                           // every other CTA's total is visible now
     uint64_t total;
     digit_base[threadIdx.x] = block_exclusive_scan_256(__ldcg(row_total + threadIdx.x), &total, warp_sums);
+    if (threadIdx.x == 0) *ticket = 0;   // ready for the next pass (fused passes have no histogram kernel to do it)
 }
 
 // Stable scatter.  A CTA walks its chunk in tiles of kSortThreads * IPT keys; warp w owns the w-th
@@ -146,7 +152,7 @@ __global__ void __launch_bounds__(256) ocm_sort_scan_kernel(const uint32_t *coun
 template <int IPT>
 __global__ void __launch_bounds__(kSortThreads, IPT <= 8 ? 4 : 2)
     ocm_sort_scatter_kernel(const uint64_t *in, uint64_t *out, uint64_t n, int shift, const uint64_t *offsets,
-                            const uint64_t *digit_base, uint64_t chunk) {
+                            const uint64_t *digit_base, uint64_t chunk, uint32_t *next_counts, int chunk_shift) {
     constexpr int kWarps = kSortThreads / 32;
     constexpr int kTile = kSortThreads * IPT;
     __shared__ uint64_t skeys[kTile];
@@ -237,7 +243,12 @@ __global__ void __launch_bounds__(kSortThreads, IPT <= 8 ? 4 : 2)
             const uint32_t i = t + j * kSortThreads;
             if (i < tile_n) {
                 const uint64_t kk = skeys[i];
-                out[gpos[digit_of(kk, shift)] + i] = kk;
+                const uint64_t pos = gpos[digit_of(kk, shift)] + i;
+                out[pos] = kk;
+                // fused mode (small inputs, chunk = 1 << chunk_shift): count the key for the next pass's histogram
+                // of the CTA that will own position pos - saves that pass's histogram launch
+                if (next_counts)
+                    atomicAdd(&next_counts[(uint64_t)digit_of(kk, shift + 8) * gridDim.x + (pos >> chunk_shift)], 1u);
             }
         }
     }
@@ -249,33 +260,59 @@ constexpr size_t sort_scratch_for(int ctas) {
     return (size_t)kRadix * ctas * (sizeof(uint32_t) + sizeof(uint64_t)) + 2 * (size_t)kRadix * sizeof(uint64_t) + 8;
 }
 
+// Small inputs are launch-bound (24 launches of ~5.5 us): up to this many keys the scatter kernel of pass p also
+// builds the histogram of pass p+1 with global atomics (one tile of 2048 keys per CTA, so the CTA that will own an
+// output position is position >> 11), which removes seven of the eight histogram launches.  For large inputs
+// 2^26 atomics per pass would cost more than the separate histogram kernel's extra read.
+constexpr uint64_t kSortFuseMaxKeys = 1ull << 19;
+constexpr int kSortFuseChunkShift = 11;
+static bool sort_fused(uint64_t n) {
+    static const bool enabled = [] {
+        const char *e = getenv("OCM_SORT_FUSE");   // 0 disables the fused small-input mode
+        return !(e && atoi(e) == 0);
+    }();
+    return enabled && n <= kSortFuseMaxKeys;
+}
+
 size_t sort_scratch_bytes(uint64_t n, int *ctas_out) {
     // one scatter tile (2048 keys) per CTA until the grid is four CTAs per SM, longer chunks after that
     int ctas = (int)std::min<uint64_t>(std::max<uint64_t>((n + 2047) / 2048, 1), (uint64_t)num_sms() * 4);
     if (ctas_out) *ctas_out = ctas;
-    return sort_scratch_for(ctas);
+    // fused mode keeps a second count matrix behind the regular layout
+    return sort_scratch_for(ctas) + (sort_fused(n) ? (size_t)kRadix * ctas * sizeof(uint32_t) : 0);
 }
 
 // The eight passes (hist, scan, scatter), shared by the regular and the allocation-free entry point.
-static void sort_passes(uint64_t *keys, uint64_t *tmp, uint64_t n, int ctas, void *scratch, cudaStream_t stream) {
+// fuse: see kSortFuseMaxKeys; needs ctas == ceil(n / 2048) and the second count matrix in the scratch.
+static void sort_passes(uint64_t *keys, uint64_t *tmp, uint64_t n, int ctas, void *scratch, cudaStream_t stream, bool fuse) {
     uint32_t *counts = static_cast<uint32_t *>(scratch);
     uint64_t *offsets = reinterpret_cast<uint64_t *>(static_cast<uint8_t *>(scratch) + (size_t)kRadix * ctas * sizeof(uint32_t));
     uint64_t *row_total = offsets + (size_t)kRadix * ctas;
     uint64_t *digit_base = row_total + kRadix;
     unsigned int *ticket = reinterpret_cast<unsigned int *>(digit_base + kRadix);
-    const uint64_t chunk = ((n + ctas - 1) / ctas + kSortThreads - 1) / kSortThreads * kSortThreads;
+    uint32_t *counts2 = reinterpret_cast<uint32_t *>(reinterpret_cast<uint8_t *>(ticket) + 8);   // fused mode only
+    const uint64_t chunk = fuse ? (1ull << kSortFuseChunkShift)
+                                : ((n + ctas - 1) / ctas + kSortThreads - 1) / kSortThreads * kSortThreads;
     uint64_t *a = keys, *b = tmp;
+    uint32_t *cur = counts, *nxt = counts2;
     static const int ipt = [] {
         const char *e = getenv("OCM_SORT_IPT");   // keys per thread per tile of the scatter: 8 (default) or 16
         return e && atoi(e) == 16 ? 16 : 8;
     }();
     for (int pass = 0; pass < 8; ++pass) {
         const int shift = pass * 8;
-        ocm_sort_hist_kernel<<<ctas, kSortThreads, 0, stream>>>(a, n, shift, counts, chunk, ticket);
-        ocm_sort_scan_kernel<<<kRadix, 256, 0, stream>>>(counts, offsets, row_total, digit_base, ctas, ticket);
-        if (ipt == 16) ocm_sort_scatter_kernel<16><<<ctas, kSortThreads, 0, stream>>>(a, b, n, shift, offsets, digit_base, chunk);
-        else ocm_sort_scatter_kernel<8><<<ctas, kSortThreads, 0, stream>>>(a, b, n, shift, offsets, digit_base, chunk);
+        const bool feed_next = fuse && pass < 7;   // this pass's scatter counts the digits of the next pass
+        if (!fuse || pass == 0) ocm_sort_hist_kernel<<<ctas, kSortThreads, 0, stream>>>(a, n, shift, cur, chunk, ticket);
+        ocm_sort_scan_kernel<<<kRadix, 256, 0, stream>>>(cur, offsets, row_total, digit_base, ctas, ticket,
+                                                        feed_next ? nxt : nullptr);
+        if (ipt == 16)
+            ocm_sort_scatter_kernel<16><<<ctas, kSortThreads, 0, stream>>>(a, b, n, shift, offsets, digit_base, chunk,
+                                                                           feed_next ? nxt : nullptr, kSortFuseChunkShift);
+        else
+            ocm_sort_scatter_kernel<8><<<ctas, kSortThreads, 0, stream>>>(a, b, n, shift, offsets, digit_base, chunk,
+                                                                          feed_next ? nxt : nullptr, kSortFuseChunkShift);
         std::swap(a, b);
+        if (fuse) std::swap(cur, nxt);
     }
 }
 
@@ -285,8 +322,9 @@ cudaError_t launch_sort_u64(uint64_t *keys, uint64_t *tmp, uint64_t n, void *scr
     if (n < 2) return cudaSuccess;
     int ctas = 0;
     if (scratch_bytes < sort_scratch_bytes(n, &ctas)) return cudaErrorInvalidValue;
-    sort_passes(keys, tmp, n, ctas, scratch, stream);
-    if (launches) *launches += 8 * 3;
+    const bool fuse = sort_fused(n);
+    sort_passes(keys, tmp, n, ctas, scratch, stream, fuse);
+    if (launches) *launches += fuse ? 3 + 7 * 2 : 8 * 3;
     return cudaGetLastError();
 }
 
@@ -357,7 +395,7 @@ extern "C" int ocmk_sort_u64_noalloc(uint64_t *keys, uint64_t *tmp, uint64_t n, 
         g_sort_scratch_addr[dev].store(scratch, std::memory_order_release);
     }
     const int ctas = (int)std::min<uint64_t>(std::max<uint64_t>((n + 8191) / 8192, 1), (uint64_t)kNoAllocMaxCtas);
-    sort_passes(keys, tmp, n, ctas, scratch, static_cast<cudaStream_t>(stream));
+    sort_passes(keys, tmp, n, ctas, scratch, static_cast<cudaStream_t>(stream), /*fuse=*/false);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         LOGE("ocmk_sort_u64_noalloc: launch failed: %s", cudaGetErrorString(e));

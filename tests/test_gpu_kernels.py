@@ -213,8 +213,10 @@ def test_gups_matches_oracle_and_is_involution():
     assert all(int(s.abs().sum()) == 0 for s in slabs)
 
 
-@pytest.mark.parametrize("n", [1, 2, 1000, 8192, (1 << 20) + 17])
+@pytest.mark.parametrize("n", [1, 2, 1000, 2048, 2049, 8192, 100_003, 1 << 19, (1 << 19) + 1, (1 << 20) + 17])
 def test_sort_u64_matches_oracle(n):
+    """Sizes on both sides of the fused small-input mode (<= 2^19 keys: the scatter kernel of a pass builds the
+    next pass's histogram) and of the one-tile-per-CTA boundary."""
     g = torch.Generator(device="cuda")
     g.manual_seed(n)
     keys = torch.randint(0, 2**62, (n,), dtype=torch.int64, device="cuda", generator=g)
