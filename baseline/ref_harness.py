@@ -45,6 +45,18 @@ def _free_ports(n):
     return ports
 
 
+def _have_cuda_device() -> bool:
+    """True when the CUDA driver reports at least one device (asked directly: no torch import, no /dev guessing)."""
+    import ctypes
+
+    try:
+        cu = ctypes.CDLL("libcuda.so.1")
+        n = ctypes.c_int(0)
+        return cu.cuInit(0) == 0 and cu.cuDeviceGetCount(ctypes.byref(n)) == 0 and n.value > 0
+    except OSError:
+        return False
+
+
 def unavailable(why: str) -> None:
     print(json.dumps({"impl": "reference", "unavailable": why}), flush=True)
 
@@ -55,7 +67,7 @@ def main(args) -> None:
                            "reference is impossible: it has neither setup.py nor pyproject.toml")
     if shutil.which("unshare") is None:
         return unavailable("unshare(1) missing: cannot give each reference daemon its own hostname/IPC namespace")
-    if not os.path.exists("/dev/nvidiactl"):
+    if not _have_cuda_device():
         return unavailable("no CUDA device on this machine: the reference ignores every cudaMalloc/cudaMemcpy error "
                            "except out-of-memory (src/lib.c:240-249,640), so its GPU copy would 'run' and time nothing")
     rank = int(os.environ.get("RANK", "0"))
