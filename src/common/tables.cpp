@@ -444,17 +444,57 @@ size_t pool_count_live(TableHeader *h, int tier) {
     return n;
 }
 
-int64_t mc_range_alloc(ClusterTable *c, uint64_t bytes) {
+int64_t mc_range_alloc(ClusterTable *c, uint64_t bytes, int owner_pid, int owner_rank) {
     if (c->mc_state.load(std::memory_order_acquire) != MC_READY || !bytes) return -1;
     const uint64_t n = (bytes + kMcGranule - 1) / kMcGranule;
     if (n > c->mc_n_granules) return -1;
     uint64_t start = find_run(c->mc_bitmap, 0, c->mc_n_granules, n);
-    return start == UINT64_MAX ? -1 : (int64_t)(start * kMcGranule);
+    if (start == UINT64_MAX) return -1;
+    c->mc_scrubbed[start].store(0, std::memory_order_relaxed);
+    c->mc_owner[start].store(owner_pid > 0 ? mc_owner_pack(owner_pid, (uint32_t)n, owner_rank, MC_RANGE_OWNED) : 0,
+                             std::memory_order_release);
+    return (int64_t)(start * kMcGranule);
 }
 
 void mc_range_free(ClusterTable *c, uint64_t offset, uint64_t bytes) {
     const uint64_t n = (bytes + kMcGranule - 1) / kMcGranule;
+    c->mc_owner[offset / kMcGranule].store(0, std::memory_order_release);
     bitmap_clear(c->mc_bitmap, offset / kMcGranule, n);
+}
+
+size_t mc_mark_dead(ClusterTable *c, int rank, bool (*pred)(int pid)) {
+    size_t marked = 0;
+    for (uint32_t g = 0; g < c->mc_n_granules && g < kMcMaxGranules; ++g) {
+        uint64_t w = c->mc_owner[g].load(std::memory_order_acquire);
+        if (mc_owner_state(w) != MC_RANGE_OWNED || mc_owner_rank(w) != rank || !pred(mc_owner_pid(w))) continue;
+        const uint64_t dead = mc_owner_pack(mc_owner_pid(w), mc_owner_granules(w), rank, MC_RANGE_DEAD);
+        if (c->mc_owner[g].compare_exchange_strong(w, dead, std::memory_order_acq_rel)) ++marked;
+    }
+    return marked;
+}
+
+size_t mc_dead_ranges(ClusterTable *c, int rank, std::vector<std::pair<uint32_t, uint32_t>> *out) {
+    size_t found = 0;
+    for (uint32_t g = 0; g < c->mc_n_granules && g < kMcMaxGranules; ++g) {
+        const uint64_t w = c->mc_owner[g].load(std::memory_order_acquire);
+        if (mc_owner_state(w) != MC_RANGE_DEAD) continue;
+        if (c->mc_scrubbed[g].load(std::memory_order_acquire) & (1ull << rank)) continue;
+        out->emplace_back(g, mc_owner_granules(w));
+        ++found;
+    }
+    return found;
+}
+
+bool mc_range_scrubbed(ClusterTable *c, int rank, uint32_t start) {
+    const uint64_t w = c->mc_owner[start].load(std::memory_order_acquire);
+    if (mc_owner_state(w) != MC_RANGE_DEAD) return false;
+    const uint64_t all = c->n_ranks >= 64 ? ~0ull : ((1ull << c->n_ranks) - 1);
+    const uint64_t before = c->mc_scrubbed[start].fetch_or(1ull << rank, std::memory_order_acq_rel);
+    if ((before | (1ull << rank)) != all || (before & (1ull << rank))) return false;
+    // we completed the set: the range is zero on every GPU and goes back to the bitmap
+    c->mc_owner[start].store(0, std::memory_order_release);
+    bitmap_clear(c->mc_bitmap, start, mc_owner_granules(w));
+    return true;
 }
 
 // ---------------------------------------------------------------- cluster --

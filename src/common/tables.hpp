@@ -28,6 +28,7 @@
 #include <cstddef>
 #include <cstdint>
 #include <string>
+#include <utility>
 #include <vector>
 
 namespace ocm {
@@ -152,11 +153,31 @@ struct ClusterTable {
     std::atomic<uint32_t> mc_added;      // daemons that added their device
     std::atomic<uint32_t> mc_bound;      // daemons that bound their slice
     std::atomic<uint64_t> mc_bitmap[kMcMaxGranules / 64];
+    // Owner of the range that STARTS at granule g (0: none), packed by mc_owner_pack: when the owning process
+    // dies the daemon of its rank marks the range dead, every daemon zeroes its own GPU's slice and sets its bit
+    // in mc_scrubbed; the daemon that completes the set returns the range to the bitmap.
+    std::atomic<uint64_t> mc_owner[kMcMaxGranules];
+    std::atomic<uint64_t> mc_scrubbed[kMcMaxGranules];
 };
 
+enum McOwnerState : uint32_t { MC_RANGE_NONE = 0, MC_RANGE_OWNED = 1, MC_RANGE_DEAD = 2 };
+inline uint64_t mc_owner_pack(int pid, uint32_t n_granules, int rank, uint32_t state) {
+    return ((uint64_t)(uint32_t)pid << 32) | ((uint64_t)(n_granules & 0xffffu) << 16) | ((uint64_t)(rank & 0xff) << 8) | (state & 0xffu);
+}
+inline int      mc_owner_pid(uint64_t w) { return (int)(uint32_t)(w >> 32); }
+inline uint32_t mc_owner_granules(uint64_t w) { return (uint32_t)(w >> 16) & 0xffffu; }   // kMcMaxGranules = 2^14 fits
+inline int      mc_owner_rank(uint64_t w) { return (int)((w >> 8) & 0xff); }
+inline uint32_t mc_owner_state(uint64_t w) { return (uint32_t)(w & 0xff); }
+
 // Sub-allocation inside the multicast region (any process).  Returns the byte offset or -1.
-int64_t mc_range_alloc(ClusterTable *c, uint64_t bytes);
+int64_t mc_range_alloc(ClusterTable *c, uint64_t bytes, int owner_pid = 0, int owner_rank = 0);
 void    mc_range_free(ClusterTable *c, uint64_t offset, uint64_t bytes);
+// Daemon of `rank`: mark the ranges of dead owners (pred(pid) true) on that rank as MC_RANGE_DEAD.  Returns how many.
+size_t  mc_mark_dead(ClusterTable *c, int rank, bool (*pred)(int pid));
+// Any daemon: the dead ranges `rank` has not zeroed yet, as (start granule, granules).
+size_t  mc_dead_ranges(ClusterTable *c, int rank, std::vector<std::pair<uint32_t, uint32_t>> *out);
+// `rank` has zeroed its slice of the dead range at `start`; frees the range when every rank has.  True if freed.
+bool    mc_range_scrubbed(ClusterTable *c, int rank, uint32_t start);
 
 uint64_t default_granule(uint64_t pool_bytes, Tier tier);
 inline std::atomic<uint64_t> *table_bitmap(TableHeader *h, int tier) {

@@ -901,6 +901,15 @@ void Daemon::reclaim_dead() {
         Region *regs = table_regions(tbl_, t);
         for (auto &b : got) note_free(rank_, t, regs[b.region].bytes);
     }
+    // multicast ranges of this rank's dead applications: mark them; every daemon's scrubber zeroes its own slice
+    if (mc_bytes_ && gpu_ >= 0) {
+        ClusterTable *ct = shared_cluster();
+        if (ct && ct->mc_state.load(std::memory_order_acquire) == MC_READY) {
+            mc_cluster_.store(ct, std::memory_order_release);
+            size_t n = mc_mark_dead(ct, rank_, [](int pid) { return pid_is_dead(pid, 0, nullptr); });
+            if (n) LOGI("%zu multicast range(s) of dead owners marked for scrubbing", n);
+        }
+    }
 }
 
 void Daemon::on_timer() {
@@ -951,6 +960,8 @@ void Daemon::on_timer() {
 void Daemon::scrub_loop() {
     if (gpu_ >= 0) cudaSetDevice(gpu_);
     std::vector<DirtyBlock> blocks;
+    std::vector<std::pair<uint32_t, uint32_t>> mc_dead;
+    uint64_t last_mc_scan_ns = 0;
     while (!stop_.load(std::memory_order_relaxed)) {
         bool worked = false;
         if (tbl_) {
@@ -974,6 +985,25 @@ void Daemon::scrub_loop() {
                     scrubbed_bytes_.fetch_add(b.bytes, std::memory_order_relaxed);
                     pool_release_scrubbed(tbl_, t, b.region);
                 }
+            }
+        }
+        // multicast ranges whose owner died: zero OUR GPU's slice; the daemon that finishes last frees the range
+        ClusterTable *ct = mc_cluster_.load(std::memory_order_acquire);
+        if (ct && gpu_pool_.ptr && tbl_ && now_ns() - last_mc_scan_ns > 50ull * 1000000ull) {
+            last_mc_scan_ns = now_ns();
+            mc_dead.clear();
+            if (mc_dead_ranges(ct, rank_, &mc_dead)) {
+                char *tail = (char *)gpu_pool_.ptr + tbl_->mc_tail_offset;
+                for (auto &r : mc_dead)
+                    ocmk::launch_fill(tail + (uint64_t)r.first * kMcGranule, (uint64_t)r.second * kMcGranule, 0,
+                                      (cudaStream_t)scrub_stream_);
+                cudaStreamSynchronize((cudaStream_t)scrub_stream_);
+                for (auto &r : mc_dead) {
+                    scrubbed_bytes_.fetch_add((uint64_t)r.second * kMcGranule, std::memory_order_relaxed);
+                    if (mc_range_scrubbed(ct, rank_, r.first))
+                        LOGI("multicast range at granule %u (%u granules) reclaimed from a dead owner", r.first, r.second);
+                }
+                worked = true;
             }
         }
         if (!worked) usleep(300);

@@ -117,6 +117,9 @@ class Daemon {
     uint64_t mc_bytes_ = 0, mc_tail_off_ = 0;
     bool mc_added_ = false, mc_bound_ = false, mc_done_ = false;
     ShmMapping cluster_peer_map_;
+    // set by the main thread once the multicast region is READY; the scrubber thread zeroes this rank's slice of
+    // ranges whose owner died (tables.hpp: mc_owner / mc_scrubbed)
+    std::atomic<ClusterTable *> mc_cluster_{nullptr};
 };
 
 uint64_t now_ns();

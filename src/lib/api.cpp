@@ -660,7 +660,7 @@ ocm_alloc_t ocm_alloc_ex(const struct ocm_alloc_params_ex *p) {
         a->stripes.resize(N);
         // replicated: prefer the NVLS multicast region (one range, same offset on every GPU)
         if (kind == OCM_REPLICATED_GPU && ensure_mc()) {
-            int64_t off = mc_range_alloc(c.cluster, per);
+            int64_t off = mc_range_alloc(c.cluster, per, (int)getpid(), c.rank);   // owner-tracked: reclaimed if we die
             bool ok = off >= 0;
             for (int r = 0; r < N && ok; ++r) {
                 RankView *v = get_view(r, true);

@@ -317,6 +317,51 @@ static void t_governor() {
     CHECK(governor_add_node(c1, 0, cfg, pools) == OCM_OK);
     rq.policy = OCM_POLICY_DEFAULT; rq.orig_rank = 0;
     CHECK(governor_place(c1, rq, &a) == OCM_OK && a.remote_rank == 0 && a.tier == TIER_GPU);
+    // liveness: a rank whose heartbeat is stale is skipped; explicit requests for it report a dead daemon
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    const uint64_t now = (uint64_t)ts.tv_sec * 1000000000ull + (uint64_t)ts.tv_nsec;
+    CHECK(governor_rank_alive(c, 2) && !governor_rank_alive(c, 3));          // never beaten = alive; not joined = not
+    c->node[2].heartbeat_ns.store(now - 5000000000ull);                       // 5 s ago
+    c->node[0].heartbeat_ns.store(now);
+    CHECK(!governor_rank_alive(c, 2) && governor_rank_alive(c, 0));
+    rq.policy = OCM_POLICY_DEFAULT; rq.orig_rank = 1; rq.bytes = 1 << 20; rq.type = ALLOC_MEM_REMOTE_GPU;
+    CHECK(governor_place(c, rq, &a) == OCM_OK && a.remote_rank == 0);        // neighbour 2 is dead -> next one
+    rq.policy = OCM_POLICY_EXPLICIT; rq.remote_rank = 2;
+    CHECK(governor_place(c, rq, &a) == OCM_ENODAEMON);
+    cfg.daemon_pid = 4242;                                                     // a new daemon process re-joins as rank 2
+    c->node[2].used[TIER_GPU].store(12345);
+    CHECK(governor_add_node(c, 2, cfg, pools) == OCM_OK && governor_rank_alive(c, 2));
+    CHECK(c->node[2].used[TIER_GPU].load() == 0);                             // new incarnation: accounting restarts
+    CHECK(governor_place(c, rq, &a) == OCM_OK && a.remote_rank == 2);
+
+    // multicast ranges: owner tracking and reclamation after the owner's death (every rank zeroes its slice first)
+    c->mc_n_granules = 64;
+    c->mc_bytes = 64 * kMcGranule;
+    c->mc_state.store(MC_READY);
+    const int64_t m0 = mc_range_alloc(c, 3 * kMcGranule, 777, 1);
+    const int64_t m1 = mc_range_alloc(c, kMcGranule, 778, 0);
+    CHECK(m0 == 0 && m1 == (int64_t)(3 * kMcGranule));
+    CHECK(mc_owner_pid(c->mc_owner[0].load()) == 777 && mc_owner_granules(c->mc_owner[0].load()) == 3 &&
+          mc_owner_rank(c->mc_owner[0].load()) == 1 && mc_owner_state(c->mc_owner[0].load()) == MC_RANGE_OWNED);
+    auto dead777 = [](int pid) { return pid == 777; };
+    CHECK(mc_mark_dead(c, 0, dead777) == 0);                                  // not rank 0's application
+    CHECK(mc_mark_dead(c, 1, dead777) == 1 && mc_mark_dead(c, 1, dead777) == 0);
+    std::vector<std::pair<uint32_t, uint32_t>> dr;
+    int freed = 0;
+    for (int r = 0; r < 4; ++r) {                                             // n_ranks = 4: all four must scrub
+        dr.clear();
+        CHECK(mc_dead_ranges(c, r, &dr) == 1 && dr[0].first == 0 && dr[0].second == 3);
+        CHECK(mc_range_alloc(c, 60 * kMcGranule + 1, 1, 0) == -1 || r == 3);  // still taken while scrubbing
+        freed += mc_range_scrubbed(c, r, 0) ? 1 : 0;
+        dr.clear();
+        CHECK(mc_dead_ranges(c, r, &dr) == 0);
+    }
+    CHECK(freed == 1 && c->mc_owner[0].load() == 0);
+    CHECK(mc_range_alloc(c, 3 * kMcGranule, 779, 2) == 0);                    // the range is back
+    mc_range_free(c, 0, 3 * kMcGranule);
+    mc_range_free(c, (uint64_t)m1, kMcGranule);
+    CHECK(c->mc_owner[3].load() == 0);
 }
 
 static void t_pmsg() {

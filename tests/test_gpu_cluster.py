@@ -304,6 +304,49 @@ def test_nvls_gather_reduce(gpu_cluster):
     a.free()
 
 
+MC_LEAK = r"""
+import os, torch, oncilla_b200 as ocm
+from oncilla_b200 import api
+ocm.init()
+torch.cuda.set_device(ocm.device())
+assert api.multicast_ready(wait_s=10.0)
+a = ocm.alloc(ocm.OCM_REPLICATED_GPU, 1 << 20, 1 << 20)
+assert a.is_multicast
+a.local_tensor().fill_(0x5A); torch.cuda.synchronize(); a.put(1 << 20); torch.cuda.synchronize()
+print("LEAKED", flush=True)
+os._exit(0)                      # dies without ocm_free / ocm_tini
+"""
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="NVLS multicast needs two GPUs")
+def test_nvls_range_of_dead_application_is_reclaimed(gpu_cluster):
+    """An application dies holding a multicast range full of data: the daemon of its rank marks the range dead,
+    every daemon zeroes its own GPU's slice, the last one returns the range - the whole region is allocatable
+    again and reads back zero on every GPU."""
+    import time
+
+    from oncilla_b200 import api
+
+    if not api.multicast_ready(wait_s=10.0):
+        pytest.skip("NVLS multicast not available on this box")
+    N = ocm.num_ranks()
+    r = run_py(gpu_cluster, N - 1, MC_LEAK)
+    assert r.returncode == 0 and "LEAKED" in r.stdout, r.stdout + r.stderr
+    region = 256 << 20                                      # OCM_MC_BYTES default: only a fully free region fits this
+    a, t0 = None, time.time()
+    while time.time() - t0 < 15:
+        a = ocm.alloc(ocm.OCM_REPLICATED_GPU, 4096, region)
+        if a.is_multicast:
+            break
+        a.free()                                            # fell back to per-rank slabs: the range is not back yet
+        a = None
+        time.sleep(0.1)
+    assert a is not None, "the dead application's multicast range was never reclaimed"
+    for rk in range(N):
+        assert int(a.slab_tensor(rk).sum()) == 0            # including the bytes the dead application wrote
+    a.free()
+
+
 ATTACH_PEER = r"""
 import sys, torch
 import oncilla_b200 as ocm
