@@ -288,6 +288,50 @@ def test_share_and_attach_between_applications(cluster2, tmp_path):
     assert p["after_free"] == 8 and p["reattach"] == 8      # OCM_ESTALE
 
 
+OVERLAP_SNIPPET = r"""
+import json, random, oncilla_b200 as ocm
+ocm.init()
+rng = random.Random(99)
+live, bad, peak, failed = [], 0, 0, 0
+def overlaps(a, b):
+    return a[0] == b[0] and a[1] < b[1] + b[2] and b[1] < a[1] + a[2]
+for step in range(1500):
+    if live and (rng.random() < 0.45 or len(live) > 60):
+        h, span = live.pop(rng.randrange(len(live)))
+        h.free()
+        continue
+    n = rng.choice([1, 100, 4096, 4097, 65536, 300000, 1 << 20])
+    flags = ocm.ALLOC_NO_WINDOW | (ocm.ALLOC_SLOW_PATH if rng.random() < 0.1 else 0)
+    pol = rng.choice([ocm.POLICY_DEFAULT, ocm.POLICY_SELF, ocm.POLICY_LEAST_LOADED, ocm.POLICY_ROUND_ROBIN])
+    try:
+        h = ocm.alloc(ocm.OCM_REMOTE_HOST, 0, n, flags=flags, policy=pol)
+    except ocm.OcmError:
+        failed += 1
+        continue
+    span = (h.remote_rank, h.remote_ptr, n)
+    bad += sum(overlaps(span, s) for _, s in live)
+    t = h.remote_tensor()
+    bad += int(t.sum()) != 0                      # handed out zeroed, whatever lived there before
+    t[:] = 0xEE
+    live.append((h, span))
+    peak = max(peak, len(live))
+for h, _ in live: h.free()
+import time; time.sleep(0.3)
+left = [ocm.stats(rank=r)["pool_host_used"] for r in range(2)]
+ocm.tini()
+print("RESULT " + json.dumps({"bad": bad, "peak": peak, "failed": failed, "left": left}))
+"""
+
+
+def test_random_alloc_free_never_overlaps_and_is_zeroed(cluster2):
+    """1500 random allocations and frees (all placement policies, both paths, sizes from 1 byte to 1 MiB): no two
+    live blocks overlap, every block is handed out zeroed although each is dirtied before its free, and the pools
+    are empty afterwards."""
+    out = _ok(run_py(cluster2, 0, OVERLAP_SNIPPET))
+    res = json.loads(out.split("RESULT ", 1)[1])
+    assert res["bad"] == 0 and res["peak"] > 20 and res["left"] == [0, 0], res
+
+
 def test_three_ranks_slow_path_forwarding():
     """REQ_ALLOC from rank 1 -> placement on rank 0 -> DO_ALLOC on rank 2 -> RELEASE_APP."""
     with ocm.LocalCluster(3, host_bytes=16 << 20, extra_env={"OCM_NO_GPU": "1"}) as cl:
