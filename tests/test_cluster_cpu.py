@@ -40,6 +40,14 @@ def test_example_hello_ocm(cluster2):
     assert "pass: hello_ocm" in out and "on rank 0" in out
 
 
+def test_example_cxx_raii_layer(cluster2):
+    """examples/raii_ocm.cpp: include/oncillamem.hpp (Session / Allocation / exceptions) over the C ABI."""
+    out = _ok(run_app(cluster2, 0, [BIN / "raii_ocm"]))
+    assert "pass: raii_ocm" in out and "FAIL" not in out
+    probe = _ok(run_py(cluster2, 0, "import oncilla_b200 as ocm; ocm.init(); print('LIVE', [ocm.stats(rank=r)['allocs_live'] for r in (0, 1)]); ocm.tini()"))
+    assert "LIVE [0, 0]" in probe                                       # the destructors released everything
+
+
 def test_stat_tool(cluster2):
     """python -m oncilla_b200.stat: per-rank pool counters through MSG_STATS."""
     env = cluster2.env(0)
