@@ -40,6 +40,14 @@ def test_example_hello_ocm(cluster2):
     assert "pass: hello_ocm" in out and "on rank 0" in out
 
 
+@pytest.mark.parametrize("path", ["fast", "daemon"])
+def test_one_application_many_threads(cluster2, path):
+    """tests/cpp/ocm_mt.c: 8 threads of one process allocate, copy both ways, put into one shared block and free
+    concurrently; every byte is verified and the shared block's signal counts every copy exactly once."""
+    out = _ok(run_app(cluster2, 0, [BIN / "ocm_mt", "8", "120"], env_extra={"OCM_ALLOC_PATH": path}, timeout=300))
+    assert "pass: ocm_mt 8 threads x 120 iterations, 960 shared signals" in out and "FAIL" not in out
+
+
 def test_example_cxx_raii_layer(cluster2):
     """examples/raii_ocm.cpp: include/oncillamem.hpp (Session / Allocation / exceptions) over the C ABI."""
     out = _ok(run_app(cluster2, 0, [BIN / "raii_ocm"]))
