@@ -733,16 +733,19 @@ ocm_alloc_t ocm_alloc(ocm_alloc_param_t alloc_param) {
 int ocm_free(ocm_alloc_t a) {
     TraceRange tr_("ocm_free");
     Ctx &c = ctx();
-    if (!valid_handle(a)) {   // NULL and double frees are rejected (reference derefs first, App. B #2)
-        set_last_error(OCM_ESTALE);
-        return -1;
-    }
     {
+        // NULL, foreign pointers and double frees are rejected WITHOUT touching the memory behind the pointer: the
+        // handle must be in the set of live allocations (the reference dereferences first, App. B #2; checking
+        // the magic word of an already-deleted handle would be a use-after-free of our own)
         std::lock_guard<std::mutex> g(c.mu);
-        if (!c.allocs.erase(a)) {
+        if (!a || !c.allocs.erase(a)) {
             set_last_error(OCM_ESTALE);
             return -1;
         }
+    }
+    if (!valid_handle(a)) {
+        set_last_error(OCM_ESTALE);
+        return -1;
     }
     if (a->lib_stream_pending.load() && c.stream) {
         DeviceGuard dg(c.device);
