@@ -131,9 +131,11 @@ static void t_ring() {
 
 static TableHeader *fresh_table(std::vector<char> &buf, uint64_t gpu, uint64_t host) {
     size_t seg = table_segment_bytes(gpu, host);
-    buf.assign(seg, 0);
-    table_format(buf.data(), seg, 0, 1, 1234, gpu, host);
-    auto *h = reinterpret_cast<TableHeader *>(buf.data());
+    buf.assign(seg + 4096, 0);
+    // page-aligned like the shm segments the tables really live in (Region / SigExt are cache-line aligned types)
+    char *base = reinterpret_cast<char *>((reinterpret_cast<uintptr_t>(buf.data()) + 4095) & ~uintptr_t(4095));
+    table_format(base, seg, 0, 1, 1234, gpu, host);
+    auto *h = reinterpret_cast<TableHeader *>(base);
     CHECK(table_validate(h, seg));
     return h;
 }
