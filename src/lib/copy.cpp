@@ -217,8 +217,18 @@ int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2
             cudaStreamSynchronize(st);
         }
         const char *s = (const char *)src.ptr + src_off;
-        memcpy((char *)dst.ptr + dst_off, s, bytes);
-        if (dst2) memcpy((char *)dst2->ptr + dst2_off, s, bytes);
+        if (!dst2) {
+            memcpy((char *)dst.ptr + dst_off, s, bytes);
+        } else {
+            // two destinations: feed both from one pass over the source, a cache-sized piece at a time, so the
+            // second copy reads from L2 instead of DRAM (the reference does two full passes, src/lib.c:530-531)
+            constexpr uint64_t kPiece = 256 << 10;
+            for (uint64_t o = 0; o < bytes; o += kPiece) {
+                const uint64_t n = std::min<uint64_t>(kPiece, bytes - o);
+                memcpy((char *)dst.ptr + dst_off + o, s + o, n);
+                memcpy((char *)dst2->ptr + dst2_off + o, s + o, n);
+            }
+        }
         if (signal_cpu) signal_cpu->fetch_add(1, std::memory_order_release);
         return OCM_OK;
     }
