@@ -480,6 +480,63 @@ def test_application_survives_peer_daemon_restart(tmp_path):
         assert res["live_end"] == 0
 
 
+CKPT_SAVE = r"""
+import json, os, torch, oncilla_b200 as ocm
+from oncilla_b200 import checkpoint as ckpt
+path = os.environ["CKPT"]
+ocm.init()
+g = torch.Generator().manual_seed(11)
+a = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, (3 << 20) + 123)          # payload = far side on rank 1
+b = ocm.alloc(ocm.OCM_LOCAL_HOST, 70000)                            # payload = local memory
+a.remote_tensor().copy_(torch.randint(0, 256, (a.remote_bytes,), dtype=torch.uint8, generator=g))
+b.local_tensor().copy_(torch.randint(0, 256, (70000,), dtype=torch.uint8, generator=g))
+hdr = ckpt.save(path, {"far": a, "near": b})
+print("RESULT " + json.dumps({"entries": [[e["name"], e["bytes"]] for e in hdr["entries"]],
+                              "sum": [int(a.remote_tensor().sum()), int(b.local_tensor().sum())]}))
+os._exit(0)                                                         # the application goes away without cleaning up
+"""
+
+CKPT_LOAD = r"""
+import json, os, torch, oncilla_b200 as ocm
+from oncilla_b200 import checkpoint as ckpt
+path = os.environ["CKPT"]
+ocm.init()
+a = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, (3 << 20) + 123)
+b = ocm.alloc(ocm.OCM_LOCAL_HOST, 70000)
+res = {"zero_before": int(a.remote_tensor().sum()) == 0 and int(b.local_tensor().sum()) == 0}
+ckpt.load(path, {"far": a, "near": b})
+res["sum"] = [int(a.remote_tensor().sum()), int(b.local_tensor().sum())]
+res["names"] = [e["name"] for e in ckpt.read_header(path)["entries"]]
+errs = []
+small = ocm.alloc(ocm.OCM_LOCAL_HOST, 100)
+for what, fn in (("size", lambda: ckpt.load(path, {"near": small})), ("name", lambda: ckpt.load(path, {"nope": b}))):
+    try: fn(); errs.append(what + ":accepted")
+    except ckpt.CheckpointError: errs.append(what + ":rejected")
+raw = bytearray(open(path, "rb").read()); raw[(1 << 20) + 5000] ^= 0xFF; open(path + ".bad", "wb").write(raw)
+try: ckpt.load(path + ".bad", {"far": a}); errs.append("crc:accepted")
+except ckpt.CheckpointError: errs.append("crc:rejected")
+res["errs"] = errs
+for x in (a, b, small): x.free()
+ocm.tini()
+print("RESULT " + json.dumps(res))
+"""
+
+
+def test_checkpoint_survives_cluster_restart(tmp_path):
+    """oncilla_b200.checkpoint: payloads of a pair's far side and of a local buffer are saved, the whole cluster is
+    torn down, a new one restores them into fresh allocations; size, name and CRC mismatches are rejected."""
+    path = str(tmp_path / "state.ocm")
+    with ocm.LocalCluster(2, host_bytes=32 << 20, extra_env={"OCM_NO_GPU": "1"}) as cl:
+        out = _ok(run_py(cl, 0, CKPT_SAVE, env_extra={"CKPT": path}))
+        saved = json.loads(out.split("RESULT ", 1)[1])
+    assert saved["entries"] == [["far", (3 << 20) + 123], ["near", 70000]]
+    with ocm.LocalCluster(2, host_bytes=32 << 20, extra_env={"OCM_NO_GPU": "1"}) as cl:       # brand-new daemons
+        out = _ok(run_py(cl, 0, CKPT_LOAD, env_extra={"CKPT": path}))
+        res = json.loads(out.split("RESULT ", 1)[1])
+    assert res["zero_before"] and res["sum"] == saved["sum"] and res["names"] == ["far", "near"]
+    assert res["errs"] == ["size:rejected", "name:rejected", "crc:rejected"]
+
+
 def test_app_death_is_reclaimed(cluster2):
     """A crashed application's regions return to the pool (TODO in reference README:68-69)."""
     code = r"""
