@@ -183,11 +183,7 @@ int Daemon::setup_ipc() {
     set_nonblocking(tcp_listen_, true);
     add_fd(tcp_listen_, FD_TCP_LISTEN);
 
-    uds_listen_ = uds_listen(uds_name(rank_));
-    if (uds_listen_ < 0) {
-        LOGE("cannot bind unix socket %s: %s", uds_name(rank_).c_str(), strerror(-uds_listen_));
-        return uds_listen_;
-    }
+    // the unix socket was bound in init() (it doubles as the "this rank is taken" lock)
     set_nonblocking(uds_listen_, true);
     add_fd(uds_listen_, FD_UDS_LISTEN);
 
@@ -231,6 +227,16 @@ int Daemon::init() {
     sigaddset(&mask, SIGINT);
     sigaddset(&mask, SIGTERM);
     pthread_sigmask(SIG_BLOCK, &mask, nullptr);
+
+    // Claim the rank first: the abstract unix socket is exclusive and disappears with its process, so it cannot be
+    // stale.  Everything after this replaces leftovers of a DEAD predecessor (tables, host pool, message queue) -
+    // which must never happen to a live daemon that someone started a duplicate of.
+    uds_listen_ = uds_listen(uds_name(rank_));
+    if (uds_listen_ < 0) {
+        LOGE("rank %d of namespace '%s' is already served by a running daemon (unix socket %s: %s)", rank_,
+             ns_tag().c_str(), uds_name(rank_).c_str(), strerror(-uds_listen_));
+        return uds_listen_;
+    }
 
     int r = setup_pools();
     if (r) return r;

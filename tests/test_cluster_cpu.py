@@ -537,6 +537,44 @@ def test_checkpoint_survives_cluster_restart(tmp_path):
     assert res["errs"] == ["size:rejected", "name:rejected", "crc:rejected"]
 
 
+def test_duplicate_daemon_cannot_hurt_a_live_cluster(cluster2):
+    """Starting a second daemon for a rank that is being served fails at once - before it replaces the live
+    daemon's tables, host pool or message queue."""
+    from oncilla_b200 import _native
+
+    for rank in (0, 1):
+        r = subprocess.run([str(_native.DAEMON_PATH), cluster2.nodefile], env=cluster2.env(rank), capture_output=True,
+                           text=True, timeout=30)
+        assert r.returncode != 0 and "already served by a running daemon" in (r.stdout + r.stderr)
+    out = _ok(run_py(cluster2, 1, PLACE_SNIPPET))
+    res = json.loads(out.split("RESULT ", 1)[1])
+    assert res["fast"] == [0, True] and res["daemon"] == [0, True], res
+
+
+def test_cleanup_removes_only_what_dead_daemons_left(cluster2):
+    """python -m oncilla_b200.cleanup: segments and queues of SIGKILLed daemons go, a live cluster stays intact."""
+    from oncilla_b200 import cleanup
+
+    doomed = ocm.LocalCluster(2, host_bytes=8 << 20, extra_env={"OCM_NO_GPU": "1"}, ns=f"doomed{os.getpid()}")
+    doomed.start()
+    ns = doomed.ns
+    try:
+        assert cleanup.sweep(ns) == []                                  # alive: nothing to do
+        for r in (1, 0):
+            doomed.kill(r)                                              # SIGKILL: no chance to unlink anything
+        left = sorted(p.name for p in cleanup.SHM.iterdir() if p.name.startswith(f"ocm_{ns}_"))
+        assert f"ocm_{ns}_tbl_r0" in left and f"ocm_{ns}_host_r1" in left and f"ocm_{ns}_cluster" in left
+        assert set(cleanup.sweep(ns, dry_run=True)) >= set(left)
+        removed = cleanup.sweep(ns)
+        assert set(removed) >= set(left) and f"/ocm_mq_{ns}_daemon" in removed
+        assert not [p for p in cleanup.SHM.iterdir() if p.name.startswith(f"ocm_{ns}_")]
+    finally:
+        doomed.stop()
+    assert cleanup.sweep(cluster2.ns) == []                             # the fixture's live cluster is untouched
+    out = _ok(run_py(cluster2, 0, "import oncilla_b200 as ocm; ocm.init(); a = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 4096); a.put(); a.free(); ocm.tini(); print('STILL_OK')"))
+    assert "STILL_OK" in out
+
+
 def test_app_death_is_reclaimed(cluster2):
     """A crashed application's regions return to the pool (TODO in reference README:68-69)."""
     code = r"""
