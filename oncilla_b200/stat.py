@@ -42,6 +42,20 @@ def main(argv=None) -> int:
     if "--json" in argv:
         print(json.dumps(rows))
         return 0
+    if "--prometheus" in argv:
+        # text exposition format: scrape it from a cron job / node_exporter textfile collector
+        print("# TYPE ocm_rank_up gauge")
+        for s in rows:
+            print(f'ocm_rank_up{{rank="{s["rank"]}"}} {1 if s["reachable"] else 0}')
+        for key, help_ in (("pool_gpu_bytes", "HBM pool capacity"), ("pool_gpu_used", "HBM pool bytes in use"),
+                           ("pool_host_bytes", "pinned host pool capacity"), ("pool_host_used", "pinned host pool bytes in use"),
+                           ("allocs_live", "live blocks"), ("allocs_total", "allocations since start"),
+                           ("frees_total", "frees since start")):
+            print(f"# HELP ocm_{key} {help_}\n# TYPE ocm_{key} {'counter' if key.endswith('_total') else 'gauge'}")
+            for s in rows:
+                if s["reachable"]:
+                    print(f'ocm_{key}{{rank="{s["rank"]}"}} {s[key]}')
+        return 0
     print(f"{'rank':>4}  {'HBM pool':>10} {'used':>10}  {'host pool':>10} {'used':>10}  {'live':>6} {'allocs':>8} {'frees':>8}")
     for s in rows:
         if not s["reachable"]:

@@ -68,6 +68,10 @@ def test_stat_tool(cluster2):
     assert all(x["pool_host_bytes"] == 32 << 20 for x in rows)
     r = subprocess.run([sys.executable, "-m", "oncilla_b200.stat"], env=env, capture_output=True, text=True, timeout=60)
     assert r.returncode == 0 and "host pool" in r.stdout and "32.0 MiB" in r.stdout
+    r = subprocess.run([sys.executable, "-m", "oncilla_b200.stat", "--prometheus"], env=env, capture_output=True,
+                       text=True, timeout=60)
+    assert r.returncode == 0 and 'ocm_rank_up{rank="1"} 1' in r.stdout
+    assert f'ocm_pool_host_bytes{{rank="0"}} {32 << 20}' in r.stdout and "# TYPE ocm_allocs_total counter" in r.stdout
 
 
 API_SNIPPET = r"""
