@@ -35,6 +35,26 @@ def test_graft_entry_has_build_and_smoke():
     assert callable(g.build) and callable(g.smoke)
 
 
+def test_checkpoint_header_rejects_garbage(tmp_path):
+    """Files that are not checkpoints (or are cut off / tampered with in the header) are refused before any data moves."""
+    import struct
+
+    from oncilla_b200 import checkpoint as ckpt
+
+    cases = {
+        "empty": b"",
+        "wrong_magic": b"NOTOCMCK" + struct.pack("<Q", 10) + b"{}" * 5,
+        "huge_header": ckpt.MAGIC + struct.pack("<Q", 1 << 40),
+        "not_json": ckpt.MAGIC + struct.pack("<Q", 6) + b"\xff\xfe{{{{",
+        "missing_keys": ckpt.MAGIC + struct.pack("<Q", 2) + b"{}",
+    }
+    for name, blob in cases.items():
+        p = tmp_path / name
+        p.write_bytes(blob)
+        with pytest.raises(ckpt.CheckpointError):
+            ckpt.read_header(str(p))
+
+
 @pytest.mark.gpu
 def test_bench_json_contract_on_gpu():
     """One short device-timed run: every key the driver reads is present and sane."""
