@@ -86,19 +86,25 @@ class TorchrunCluster:
         self.rank = int(os.environ.get("RANK", "0"))
         self.local = int(os.environ.get("LOCAL_RANK", str(self.rank)))
         self.world = int(os.environ.get("WORLD_SIZE", "1"))
-        torch.cuda.set_device(self.local)
+        self.gpu = torch.cuda.is_available()       # without a GPU: host tiers only, gloo for the control plane
+        if self.gpu:
+            torch.cuda.set_device(self.local)
         if self.world > 1:
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-            dist.init_process_group(self.backend, device_id=torch.device(f"cuda:{self.local}"))
+            if self.gpu:
+                dist.init_process_group(self.backend, device_id=torch.device(f"cuda:{self.local}"))
+            else:
+                dist.init_process_group("gloo")
         tag = os.environ.get("MASTER_PORT", str(os.getpid()))
         shared = Path(f"/tmp/ocm_job_{tag}")
         nodefile = shared / "nodefile"
         if self.rank == 0:
             shared.mkdir(parents=True, exist_ok=True)
-            write_nodefile(nodefile, self.world, gpus=list(range(self.world)), gpu_bytes=self.gpu_bytes,
-                           host_bytes=self.host_bytes)
+            write_nodefile(nodefile, self.world, gpus=list(range(self.world)) if self.gpu else None,
+                           gpu_bytes=self.gpu_bytes if self.gpu else None, host_bytes=self.host_bytes)
         self.barrier()
-        self.cl = LocalCluster(self.world, ns=f"job{tag}", nodefile=str(nodefile), ranks=[self.rank])
+        self.cl = LocalCluster(self.world, ns=f"job{tag}", nodefile=str(nodefile), ranks=[self.rank],
+                               extra_env=None if self.gpu else {"OCM_NO_GPU": "1"})
         if self.rank == 0:
             self.cl.start()
         self.barrier()
@@ -106,7 +112,10 @@ class TorchrunCluster:
             self.cl.start()
         self.barrier()
         self.cl.apply_env(self.rank)
-        os.environ["OCM_DEVICE"] = str(self.local)
+        if self.gpu:
+            os.environ["OCM_DEVICE"] = str(self.local)
+        else:
+            os.environ["OCM_NO_GPU"] = "1"
         api.init()
         return self.rank, self.world
 

@@ -541,6 +541,18 @@ def test_checkpoint_survives_cluster_restart(tmp_path):
     assert res["errs"] == ["size:rejected", "name:rejected", "crc:rejected"]
 
 
+def test_torchrun_cluster_all_to_all_over_shared_blocks():
+    """Three processes under torchrun (gloo, no GPU): TorchrunCluster brings up one daemon per rank, every rank shares
+    a receive block, attaches to the others' and writes its slot everywhere; signals count every sender."""
+    env = {k: v for k, v in os.environ.items() if not k.startswith("OCM_")}
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=3",
+                        "--master-addr", "127.0.0.1", "--master-port", "29933", str(REPO / "tests" / "torchrun_exchange.py")],
+                       env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-3000:]
+    res = json.loads(r.stdout.split("RESULT ", 1)[1].splitlines()[0])
+    assert res == [[True, 1, 3], [True, 2, 3], [True, 0, 3]], res
+
+
 def test_duplicate_daemon_cannot_hurt_a_live_cluster(cluster2):
     """Starting a second daemon for a rank that is being served fails at once - before it replaces the live
     daemon's tables, host pool or message queue."""
