@@ -925,7 +925,10 @@ void Daemon::on_timer() {
     uint64_t now = now_ns();
     tbl_->heartbeat_ns.store(now, std::memory_order_relaxed);
     if (joined_) {   // the placement code of every process reads this one (governor_rank_alive)
-        if (ClusterTable *ct = shared_cluster()) ct->node[rank_].heartbeat_ns.store(now, std::memory_order_relaxed);
+        if (ClusterTable *ct = shared_cluster()) {
+            ct->node[rank_].heartbeat_ns.store(now, std::memory_order_relaxed);
+            hb_cluster_.store(ct, std::memory_order_release);
+        }
     }
     if (!joined_) {
         bool waiting = false;
@@ -967,9 +970,18 @@ void Daemon::scrub_loop() {
     if (gpu_ >= 0) cudaSetDevice(gpu_);
     std::vector<DirtyBlock> blocks;
     std::vector<std::pair<uint32_t, uint32_t>> mc_dead;
-    uint64_t last_mc_scan_ns = 0;
+    uint64_t last_mc_scan_ns = 0, last_beat_ns = 0;
     while (!stop_.load(std::memory_order_relaxed)) {
         bool worked = false;
+        // second source of the liveness heartbeat (see hb_cluster_): "this process is alive", whatever the main
+        // loop is doing right now
+        const uint64_t t_now = now_ns();
+        if (t_now - last_beat_ns > 10ull * 1000000ull) {
+            last_beat_ns = t_now;
+            if (tbl_) tbl_->heartbeat_ns.store(t_now, std::memory_order_relaxed);
+            if (ClusterTable *hc = hb_cluster_.load(std::memory_order_acquire))
+                hc->node[rank_].heartbeat_ns.store(t_now, std::memory_order_relaxed);
+        }
         if (tbl_) {
             for (int t = 0; t < TIER_COUNT; ++t) {
                 blocks.clear();

@@ -120,6 +120,9 @@ class Daemon {
     // set by the main thread once the multicast region is READY; the scrubber thread zeroes this rank's slice of
     // ranges whose owner died (tables.hpp: mc_owner / mc_scrubbed)
     std::atomic<ClusterTable *> mc_cluster_{nullptr};
+    // cluster table for the heartbeat (set once joined).  The scrubber thread beats too, so that a main loop that
+    // is busy for a while (multicast bring-up, a long driver call) does not make a live rank look dead.
+    std::atomic<ClusterTable *> hb_cluster_{nullptr};
 };
 
 uint64_t now_ns();
