@@ -5,7 +5,10 @@
  * clock lives here, outside the reference code.  Same metric and shapes as
  * bench.py's own arm:
  *   copy   : K x ocm_copy(dest = "remote" pair, src = GPU allocation, SIZE bytes)
- *   e2e    : K x ocm_copy(dest = "remote" pair, src = host allocation, SIZE bytes)
+ *   e2e    : K x { ocm_copy(dest = GPU allocation, src = host allocation)   -- cudaMemcpy H2D, reference src/lib.c:550-558
+ *                  ocm_copy(dest = "remote" pair, src = GPU allocation) }  -- cudaMemcpy D2H + ib_write, src/lib.c:643-649
+ *            (host -> local GPU -> remote: the same end-to-end path as bench.py's own arm)
+ *   h2r    : K x ocm_copy(dest = "remote" pair, src = host allocation, SIZE bytes), all on the CPU side
  *   put/get: K x ocm_copy_onesided (the reference's own BW test shape, test/ocm_test.c:323-425)
  *   alloc  : p50 of ocm_alloc / ocm_free for the remote kind
  * Prints one JSON object.   Usage: ref_bench <size_bytes> <steps> <warmup> <alloc_iters>
@@ -63,7 +66,7 @@ int main(int argc, char **argv) {
     struct ocm_alloc_params ap;
     struct ocm_params cp;
     ocm_alloc_t gpu, host, rem;
-    double t0, t1, copy_s, e2e_s, put_s = 0, get_s = 0, *lat;
+    double t0, t1, copy_s, e2e_s, h2r_s, put_s = 0, get_s = 0, *lat;
     int i, have_pair;
     void *hb;
     size_t hl;
@@ -136,6 +139,16 @@ int main(int argc, char **argv) {
     for (i = 0; i < steps; ++i)
         if (ocm_copy(rem, host, &cp)) { printf("{\"error\": \"ocm_copy host->remote failed\"}\n"); return 1; }
     t1 = now_s();
+    h2r_s = t1 - t0;
+
+    for (i = 0; i < 2; ++i) { ocm_copy(gpu, host, &cp); ocm_copy(rem, gpu, &cp); }
+    t0 = now_s();
+    for (i = 0; i < steps; ++i)
+        if (ocm_copy(gpu, host, &cp) || ocm_copy(rem, gpu, &cp)) {
+            printf("{\"error\": \"ocm_copy host->gpu->remote failed\"}\n");
+            return 1;
+        }
+    t1 = now_s();
     e2e_s = t1 - t0;
 
     if (have_pair) {
@@ -152,9 +165,9 @@ int main(int argc, char **argv) {
         get_s = t1 - t0;
     }
 
-    printf("{\"size\": %llu, \"steps\": %d, \"granted_kind\": %d, \"copy_s\": %.9f, \"e2e_s\": %.9f, \"put_s\": %.9f, "
+    printf("{\"size\": %llu, \"steps\": %d, \"granted_kind\": %d, \"copy_s\": %.9f, \"e2e_s\": %.9f, \"h2r_s\": %.9f, \"put_s\": %.9f, "
            "\"get_s\": %.9f, \"alloc_p50_us\": %.2f, \"alloc_iters\": %d}\n",
-           (unsigned long long)size, steps, (int)ocm_alloc_kind(rem), copy_s, e2e_s, put_s, get_s,
+           (unsigned long long)size, steps, (int)ocm_alloc_kind(rem), copy_s, e2e_s, h2r_s, put_s, get_s,
            alloc_iters ? lat[alloc_iters / 2] : -1.0, alloc_iters);
     fflush(stdout);
     /* ---- teardown, again one rank at a time ------------------------------------------------ */

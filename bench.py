@@ -1,28 +1,42 @@
 #!/usr/bin/env python
-"""Headline benchmark: ocm_copy GB/s (GPU allocation -> remote-GPU allocation) at N GPUs, plus ocm_alloc p50.
+"""Headline benchmark: ocm_copy GB/s (GPU allocation -> remote allocation on the neighbour rank) at N GPUs.
 
 Contract (driver): ``python bench.py --gpus N --steps K --warmup W`` (N > 1: launched under torchrun, one
 rank per GPU).  One step = one ``ocm_copy`` of SIZE bytes from an OCM_LOCAL_GPU allocation into an
 OCM_REMOTE_GPU pair whose far side the governor places on the neighbour rank ``(r+1) % N`` (the reference's
 policy, reference src/alloc.c:107) - at N=1 that is the rank's own pool, so the copy stays inside one HBM;
-at N >= 2 every byte crosses NVLink.  The step is ONE launch of our fused kernel (TMA bulk load, bulk stores
-to the local window and to the peer).  Timed on the device with CUDA events, max over ranks, aggregate GB/s.
+at N >= 2 every byte crosses NVLink.  The kernel that runs is ``ocm_copy_v32_kernel<dual>`` (src/kernels/copy.cu):
+256-bit LDG from the source, 256-bit STG to the local window and to the peer-mapped far side, followed by a
+one-thread ``ocm_complete_kernel`` that publishes the completion signal (2 launches per step).  Timed on the
+device with CUDA events, max over ranks, aggregate GB/s.
+
+Besides the headline the JSON line carries
+  * ``e2e``: the same copy through the blocking public API starting from pinned host memory (H2D inside), then a
+    read of the 8-byte completion counter the GPU wrote to host memory;
+  * ``curve``: put / get / ocm_copy GB/s from 4 KiB to 4 GiB next to cudaMemcpyAsync peer copies (copy engines,
+    baseline only) in the same process on the same GPUs;
+  * ``alloc_p50_us_*``: ocm_alloc latency on both allocation paths.
 ``--impl reference`` runs the unmodified reference built under baseline/_ref for the same metric.
 """
 from __future__ import annotations
 
 import argparse
+import ctypes
 import json
 import os
-import statistics
 import sys
 import time
 from pathlib import Path
 
 REPO = Path(__file__).resolve().parent
 sys.path.insert(0, str(REPO))
+sys.path.insert(0, str(REPO / "baseline"))
 
 SIZE_DEFAULT = 256 << 20     # > 126 MB L2: every iteration streams from/to HBM ("inputs larger than L2")
+CURVE_SIZES = [4 << 10, 64 << 10, 1 << 20, 16 << 20, 256 << 20, 1 << 30, 4 << 30]
+NVLINK_ROOFLINE_GBPS = 900.0     # BASELINE.json: NVLink 5, per GPU per direction
+NVLINK_MEASURED_GBPS = 770.0     # B200_PROFILING.md: measured peer copy per direction
+HBM_MEASURED_GBPS = 6544.0       # MEASURED_PEAKS.json (read + write bytes)
 
 
 def parse():
@@ -33,6 +47,7 @@ def parse():
     ap.add_argument("--impl", default="ocm", choices=["ocm", "reference"])
     ap.add_argument("--size", type=int, default=SIZE_DEFAULT)
     ap.add_argument("--alloc-iters", type=int, default=2000)
+    ap.add_argument("--curve-max", type=int, default=CURVE_SIZES[-1], help="largest message of the size curve (0: no curve)")
     return ap.parse_args()
 
 
@@ -73,6 +88,70 @@ def allmax(x, world):
     return float(t.item())
 
 
+def size_curve(ocm, ops, pair, big_src, world, cmax, flush):
+    """put / get / ocm_copy and the copy-engine baseline at every size; all ranks at once, max over ranks.
+
+    No address is reused inside one size (offsets rotate through the pair's ``cmax``-byte window and far side) and the
+    L2 is flushed between measurements, so small messages are not served from cache.
+    """
+    import torch
+
+    rt = ctypes.CDLL("libcudart.so.12")
+    stream = torch.cuda.current_stream()
+    sp = ctypes.c_void_p(int(stream.cuda_stream) or 1)
+    win, far = pair.local_ptr, pair.remote_ptr
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    V = ctypes.c_void_p
+
+    def offsets(size, iters):
+        step = max(size, 1 << 20)
+        span = max(cmax - size, 0) // step + 1
+        return [(i % span) * step for i in range(iters)]
+
+    def timed(fn, size, iters):
+        offs = offsets(size, iters + 3)
+        for o in offs[:3]:
+            fn(size, o)
+        flush()
+        barrier(world)
+        ev0.record()
+        for o in offs[3:]:
+            fn(size, o)
+        ev1.record()
+        barrier(world)
+        return allmax(ev0.elapsed_time(ev1), world) / iters * 1e3      # us per message
+
+    def ce(dst, src):
+        def fn(size, o):
+            if rt.cudaMemcpyAsync(V(dst + o), V(src + o), ctypes.c_size_t(size), 4, sp) != 0:    # cudaMemcpyDefault
+                raise RuntimeError("cudaMemcpyAsync peer copy failed")
+        return fn
+
+    ours = {
+        # ocm_copy(GPU allocation -> pair): source read once, stored to the window and to the far side
+        "copy": lambda size, o: ocm.copy(pair, big_src, size, src_offset=o, dest_offset=o, src_offset_2=o, dest_offset_2=o,
+                                         stream=stream),
+        "put": lambda size, o: pair.put(size, src_offset=o, dest_offset=o, stream=stream),
+        "get": lambda size, o: pair.get(size, src_offset=o, dest_offset=o, stream=stream),
+        "ce_put": ce(far, win),
+        "ce_get": ce(win, far),
+    }
+    rows = []
+    for size in [s for s in CURVE_SIZES if s <= cmax]:
+        iters = 3 if size >= 1 << 30 else 10 if size >= 64 << 20 else 40
+        row = {"bytes": size}
+        for name, fn in ours.items():
+            try:
+                us = timed(fn, size, iters)
+            except RuntimeError as e:       # the baseline, not the product, failed: report and go on
+                row[name + "_error"] = str(e)
+                continue
+            row[name + "_us"] = round(us, 2)
+            row[name + "_GBps"] = round(size / us / 1e3, 2)
+        rows.append(row)
+    return rows
+
+
 def run_ocm(args):
     import torch
     import torch.distributed as dist
@@ -80,9 +159,11 @@ def run_ocm(args):
     import oncilla_b200 as ocm
     from oncilla_b200 import ops
     from oncilla_b200.utils import ClockSampler
+    from ref_harness import METRIC
 
     rank, local, world = dist_setup(args.gpus)
     S, K, W = args.size, args.steps, max(args.warmup, 3)
+    cmax = args.curve_max
 
     # --- bring up one daemon per rank (this process starts its own) ---------------------------------
     tag = os.environ.get("MASTER_PORT", str(os.getpid()))
@@ -91,7 +172,7 @@ def run_ocm(args):
     nodefile = shared / "nodefile"
     if rank == 0:
         shared.mkdir(parents=True, exist_ok=True)
-        pool = max(4 * S, 2 << 30)
+        pool = max(4 * S, 2 << 30) + 3 * cmax + (256 << 20 if cmax else 0)
         ocm.write_nodefile(nodefile, world, gpus=list(range(world)), gpu_bytes=pool, host_bytes=max(2 * S, 512 << 20))
     barrier(world)
     cl = ocm.LocalCluster(world, ns=ns, nodefile=str(nodefile), ranks=[rank])
@@ -170,6 +251,19 @@ def run_ocm(args):
         clocks.__exit__(None, None, None)
         ok = ok and ops.verify(dst.remote_tensor(), ((0x1111 + rank) & 0xFFFFFFFFFFFFFFFF), S) == 0
 
+        # --- GB/s versus message size, next to the copy engines (BASELINE.json metric: "GB/s vs size") ----
+        curve = None
+        if cmax:
+            pair = ocm.alloc(ocm.OCM_REMOTE_GPU, cmax, cmax)
+            big_src = ocm.alloc(ocm.OCM_LOCAL_GPU, cmax)
+            assert pair.remote_rank == (rank + 1) % world
+            flush_t = src.local_tensor()
+            curve = size_curve(ocm, ops, pair, big_src, world, cmax, lambda: ops.fill(flush_t, 0x0123456789ABCDEF + rank))
+            torch.cuda.synchronize()
+            barrier(world)
+            pair.free()
+            big_src.free()
+
         # --- p50 ocm_alloc latency (fast path and daemon path) ---------------------------------------------
         def alloc_lat(flags):
             ts = []
@@ -185,24 +279,39 @@ def run_ocm(args):
         extra["verified"] = bool(ok)
 
         if rank == 0:
+            per_gpu = value / world
+            if world > 1:
+                roof = {"frac_of_roofline": round(per_gpu / NVLINK_ROOFLINE_GBPS, 3),
+                        "roofline": "NVLink 5: 900 GB/s per GPU per direction (BASELINE.json)",
+                        "frac_of_measured_peer_copy": round(per_gpu / NVLINK_MEASURED_GBPS, 3),
+                        "measured_peer_copy": "770 GB/s per direction (B200_PROFILING.md)"}
+            else:
+                roof = {"frac_of_roofline": round(per_gpu / (HBM_MEASURED_GBPS / 3), 3),
+                        "roofline": "HBM: 1 read + 2 writes per byte of 6544 GB/s measured copy bandwidth "
+                                    "(MEASURED_PEAKS.json); no byte crosses NVLink at 1 GPU"}
             result = {
-                "metric": "ocm_copy GB/s (GPU alloc -> remote-GPU alloc on neighbour rank), aggregate over ranks",
+                "metric": METRIC,
                 "value": round(value, 2), "unit": "GB/s", "n_gpus": world, "steps": K, "warmup": W,
                 "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "bytes (no arithmetic)", "data": "synthetic",
                 "config": {"model": "ocm_copy LOCAL_GPU->REMOTE_GPU", "message_bytes": S, "global_batch": world,
                            "seq_len": S, "parallelism": f"neighbour-put x{world}",
-                           "cache": "inputs larger than L2 (no flush needed)",
+                           "cache": "inputs larger than L2 (no flush needed); size curve: rotating offsets + L2 flush "
+                                    "between measurements",
                            "n1_note": "at 1 GPU the neighbour is the rank itself: HBM-local copy, no NVLink"},
                 "clocks": clocks.summary(),
                 "e2e": {"value": round(e2e, 2), "unit": "GB/s", "h2d_bytes_per_step": S, "d2h_bytes_per_step": 8,
                         "path": "ocm_copy(pinned LOCAL_HOST -> REMOTE_GPU pair), sync, then read the signal word"},
                 "gpu_launches": int(launches) * world,
-                "frac_of_roofline": round(value / world / (770.0 if world > 1 else 6544.0 / 3), 3),
-                "roofline": "770 GB/s/dir NVLink (measured)" if world > 1 else
-                            "HBM: 1 read + 2 writes per byte of 6544 GB/s measured copy BW",
-                "impl": "ocm", **extra,
+                "kernels": "ocm_copy_v32_kernel<dual> + ocm_complete_kernel per step",
+                **roof, "impl": "ocm", **extra,
             }
+            if curve is not None:
+                result["curve"] = curve
+                result["curve_note"] = ("us per message and GB/s per GPU, all ranks putting/getting at once, max over "
+                                        "ranks; copy = ocm_copy GPU allocation -> pair (window + far side), put/get = ocm_copy_onesided "
+                                        "(our kernels), ce_* = cudaMemcpyAsync "
+                                        "between the same peer-mapped buffers (copy engines, baseline only)")
         for a in (src, dst, host):
             a.free()
     finally:
@@ -216,7 +325,6 @@ def run_ocm(args):
 
 
 def run_reference(args):
-    sys.path.insert(0, str(REPO / "baseline"))
     try:
         import ref_harness
     except Exception as e:  # pragma: no cover

@@ -92,6 +92,7 @@ uint64_t first_busy(std::atomic<uint64_t> *bm, uint64_t start, uint64_t n) {
 
 // Find and claim a free run of n granules in [lo, hi).  Returns its start or UINT64_MAX.
 uint64_t find_run(std::atomic<uint64_t> *bm, uint64_t lo, uint64_t hi, uint64_t n) {
+    if (n == 0 || n > hi) return UINT64_MAX;   // an empty run would "succeed" without claiming anything
     uint64_t i = lo;
     while (i + n <= hi) {
         i = next_free(bm, i, hi);
@@ -285,8 +286,9 @@ int pool_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int rank, Bloc
     PoolDesc &p = h->pool[tier];
     if (p.n_granules == 0) return OCM_ENOMEM;
     if (bytes == 0) bytes = 1;
+    if (bytes > p.bytes) return OCM_ENOMEM;   // before any arithmetic: a huge size must not wrap to a small block
     const uint64_t n = (bytes + p.granule - 1) / p.granule;
-    if (n > p.n_granules) return OCM_ENOMEM;
+    if (n == 0 || n > p.n_granules) return OCM_ENOMEM;
     std::atomic<uint64_t> *bm = table_bitmap(h, tier);
     const uint64_t N = p.n_granules;
     uint64_t hint = p.hint.load(std::memory_order_relaxed);
@@ -445,7 +447,7 @@ size_t pool_count_live(TableHeader *h, int tier) {
 }
 
 int64_t mc_range_alloc(ClusterTable *c, uint64_t bytes, int owner_pid, int owner_rank) {
-    if (c->mc_state.load(std::memory_order_acquire) != MC_READY || !bytes) return -1;
+    if (c->mc_state.load(std::memory_order_acquire) != MC_READY || !bytes || bytes > c->mc_bytes) return -1;
     const uint64_t n = (bytes + kMcGranule - 1) / kMcGranule;
     if (n > c->mc_n_granules) return -1;
     uint64_t start = find_run(c->mc_bitmap, 0, c->mc_n_granules, n);
@@ -505,12 +507,12 @@ void cluster_format(ClusterTable *c, int n_ranks) {
 }
 
 bool cluster_reserve(ClusterTable *c, int rank, int tier, uint64_t bytes) {
-    if (rank < 0 || rank >= c->n_ranks || rank >= kMaxRanks) return false;
+    if (rank < 0 || rank >= c->n_ranks || rank >= kMaxRanks || tier < 0 || tier >= TIER_COUNT) return false;
     NodeSlot &n = c->node[rank];
     uint64_t cap = n.pool_bytes[tier];
     uint64_t u = n.used[tier].load(std::memory_order_relaxed);
     for (;;) {
-        if (u + bytes > cap) {
+        if (bytes > cap || u > cap - bytes) {   // written so that a huge request cannot wrap around
             c->rejected.fetch_add(1, std::memory_order_relaxed);
             return false;
         }
@@ -522,7 +524,7 @@ bool cluster_reserve(ClusterTable *c, int rank, int tier, uint64_t bytes) {
 }
 
 void cluster_unreserve(ClusterTable *c, int rank, int tier, uint64_t bytes) {
-    if (rank < 0 || rank >= c->n_ranks || rank >= kMaxRanks) return;
+    if (rank < 0 || rank >= c->n_ranks || rank >= kMaxRanks || tier < 0 || tier >= TIER_COUNT) return;
     NodeSlot &n = c->node[rank];
     uint64_t u = n.used[tier].load(std::memory_order_relaxed);
     for (;;) {

@@ -426,7 +426,9 @@ void Daemon::on_peer_request(int fd, Message &m) {
         m.err = do_free_local(m.u.alloc);
         break;
     case MSG_NOTE_FREE:
-        if (rank_ == 0) governor_release(cluster_, m.u.alloc.remote_rank, (int)m.u.alloc.tier, m.u.alloc.bytes);
+        // rank and tier come off the wire: cluster_unreserve checks both before it indexes the table
+        if (rank_ == 0 && m.u.alloc.tier < (uint32_t)TIER_COUNT)
+            governor_release(cluster_, m.u.alloc.remote_rank, (int)m.u.alloc.tier, m.u.alloc.bytes);
         reply = false;
         break;
     case MSG_STATS:

@@ -217,6 +217,11 @@ __global__ void ocm_complete_kernel(uint64_t *signal, uint64_t *done_flag, uint6
 }
 
 // ------------------------------------------------------------------ host ----
+std::atomic<unsigned long long> &extra_launches() {
+    static std::atomic<unsigned long long> n{0};
+    return n;
+}
+
 int num_sms(int device) {
     static int cached[64] = {0};
     int dev = device;

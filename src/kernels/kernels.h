@@ -3,6 +3,7 @@
 // be local HBM, peer HBM mapped into this process (NVLink), or pinned host
 // memory registered with CUDA - the kernels only see generic global addresses.
 #pragma once
+#include <atomic>
 #include <cstddef>
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -97,5 +98,8 @@ cudaError_t launch_sort_u64(uint64_t *keys, uint64_t *tmp, uint64_t n, void *scr
                             cudaStream_t stream, unsigned long long *launches = nullptr);
 
 int num_sms(int device = -1);
+// Launches made by entry points that live inside the kernel library (ocmk_sort_u64_noalloc, the copy server);
+// ocmk_launch_count() adds it to the library's own counters.
+std::atomic<unsigned long long> &extra_launches();
 
 } // namespace ocmk

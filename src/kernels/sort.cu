@@ -322,7 +322,8 @@ cudaError_t launch_sort_u64(uint64_t *keys, uint64_t *tmp, uint64_t n, void *scr
     if (n < 2) return cudaSuccess;
     int ctas = 0;
     if (scratch_bytes < sort_scratch_bytes(n, &ctas)) return cudaErrorInvalidValue;
-    const bool fuse = sort_fused(n);
+    // the fused small-input mode assumes one 2048-key tile per CTA (true while n/2048 <= 4 CTAs per SM)
+    const bool fuse = sort_fused(n) && (uint64_t)ctas == (n + 2047) / 2048;
     sort_passes(keys, tmp, n, ctas, scratch, stream, fuse);
     if (launches) *launches += fuse ? 3 + 7 * 2 : 8 * 3;
     return cudaGetLastError();
@@ -399,7 +400,10 @@ extern "C" int ocmk_sort_u64_noalloc(uint64_t *keys, uint64_t *tmp, uint64_t n, 
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         LOGE("ocmk_sort_u64_noalloc: launch failed: %s", cudaGetErrorString(e));
+        // the cached address belongs to a context that may be gone (cudaDeviceReset): look it up again next time
+        g_sort_scratch_addr[dev].store(nullptr, std::memory_order_release);
         return -OCM_ECUDA;
     }
+    ocmk::extra_launches().fetch_add(24, std::memory_order_relaxed);   // 8 passes x (histogram, scan, scatter)
     return 0;
 }

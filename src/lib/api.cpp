@@ -504,10 +504,12 @@ int ocm_init(void) {
                 else c.tickets = nullptr;
                 void *hw = nullptr;
                 if (!getenv("OCM_NO_SPIN_SYNC") &&
-                    cudaHostAlloc(&hw, 64, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
-                    memset(hw, 0, 64);
+                    cudaHostAlloc(&hw, kDoneSlots * kDoneSlotWords * 8, cudaHostAllocMapped | cudaHostAllocPortable) ==
+                        cudaSuccess) {
+                    memset(hw, 0, kDoneSlots * kDoneSlotWords * 8);
+                    memset(c.done_seq, 0, sizeof c.done_seq);
                     c.done_word = static_cast<uint64_t *>(hw);
-                    c.done_seq.store(0);
+                    c.done_slots_free.store(~0ull, std::memory_order_release);
                 } else {
                     cudaGetLastError();
                 }
@@ -554,6 +556,7 @@ int ocm_tini(void) {
             cudaStreamDestroy((cudaStream_t)c.stream);
         }
         if (c.tickets) cudaFree(c.tickets);
+        c.done_slots_free.store(0, std::memory_order_release);   // no thread may claim a slot from here on
         if (c.done_word) cudaFreeHost(c.done_word);
         c.done_word = nullptr;
         c.stream = nullptr;
@@ -937,7 +940,7 @@ int ocm_get_stats(struct ocm_stats *out) {
     out->bytes_host_live = c.bytes_live[TIER_HOST].load();
     out->copies = c.n_copies.load();
     out->copy_bytes = c.copy_bytes.load();
-    out->kernel_launches = c.kernel_launches;
+    out->kernel_launches = c.kernel_launches.load(std::memory_order_relaxed);
     out->fast_path_allocs = c.n_fast.load();
     out->slow_path_allocs = c.n_slow.load();
     if (RankView *v = get_view(c.rank, false)) {

@@ -52,6 +52,15 @@ static const ocmk::CopyNotify *note_kernel(bool has_signal) {
 }
 static void note_other_gpu_op(int n = 1) { t_sn.gpu_ops += n; }
 
+// Kernels enqueued by the current side_copy call on this thread; added to the process-wide counter when it returns.
+static thread_local unsigned long long launches_ = 0;
+struct LaunchFlush {
+    ~LaunchFlush() {
+        if (launches_) ctx().kernel_launches.fetch_add(launches_, std::memory_order_relaxed);
+        launches_ = 0;
+    }
+};
+
 static int cuda_err(cudaError_t e, const char *what) {
     if (e == cudaSuccess) return OCM_OK;
     LOGE("%s: %s", what, cudaGetErrorString(e));
@@ -152,14 +161,14 @@ static int try_pull_put(const Side &dst, uint64_t dst_off, const Side *dst2, uin
         e = cudaStreamWaitEvent((cudaStream_t)pe->stream, (cudaEvent_t)pe->ev_in[slot], 0);
         if (e == cudaSuccess)
             e = ocmk::launch_copy((char *)dst.ptr + dst_off, nullptr, (const char *)src.ptr + src_off, bytes, signal,
-                                  pe->tickets + slot, (cudaStream_t)pe->stream, nullptr, &c.kernel_launches);
+                                  pe->tickets + slot, (cudaStream_t)pe->stream, nullptr, &launches_);
         if (e == cudaSuccess) e = cudaEventRecord((cudaEvent_t)pe->ev_out[slot], (cudaStream_t)pe->stream);
     }
     if (e == cudaSuccess) {
         DeviceGuard dg(c.device);
         if (dst2)   // the window is local: its copy runs here, concurrently with the pull
             e = ocmk::launch_copy((char *)dst2->ptr + dst2_off, nullptr, (const char *)src.ptr + src_off, bytes, nullptr,
-                                  next_ticket(), st, nullptr, &c.kernel_launches);
+                                  next_ticket(), st, nullptr, &launches_);
         if (e == cudaSuccess) e = cudaStreamWaitEvent(st, (cudaEvent_t)pe->ev_out[slot], 0);
     }
     if (e != cudaSuccess) return cuda_err(e, "pull-mode put");
@@ -184,7 +193,7 @@ static int single_copy(const Side &dst, uint64_t dst_off, const Side &src, uint6
     *used_stream = true;
     if (dst.tier == TIER_GPU && src.tier == TIER_GPU) {
         *signalled = signal != nullptr;
-        return cuda_err(ocmk::launch_copy(d, nullptr, s, bytes, signal, next_ticket(), st, nullptr, &c.kernel_launches,
+        return cuda_err(ocmk::launch_copy(d, nullptr, s, bytes, signal, next_ticket(), st, nullptr, &launches_,
                                           note_kernel(signal != nullptr)),
                         "copy kernel");
     }
@@ -200,6 +209,7 @@ static inline bool fits(const Side &s, uint64_t off, uint64_t n) { return n <= s
 int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2_off, const Side &src, uint64_t src_off,
               uint64_t bytes, const Side *sig, void *stream, bool *used_stream) {
     Ctx &c = ctx();
+    LaunchFlush flush_launches;
     if (!dst.ptr || !src.ptr || (dst2 && !dst2->ptr)) return OCM_EINVAL;
     if (!fits(src, src_off, bytes) || !fits(dst, dst_off, bytes) || (dst2 && !fits(*dst2, dst2_off, bytes)))
         return OCM_ERANGE;
@@ -253,7 +263,7 @@ int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2
         *used_stream = true;
         err = cuda_err(ocmk::launch_copy((char *)dst.ptr + dst_off, dst2 ? (char *)dst2->ptr + dst2_off : nullptr,
                                          (const char *)src.ptr + src_off, bytes, signal, next_ticket(), st, nullptr,
-                                         &c.kernel_launches, note_kernel(signal != nullptr)),
+                                         &launches_, note_kernel(signal != nullptr)),
                        "copy kernel");
         signalled = signal != nullptr;
     } else {
@@ -293,9 +303,9 @@ static int stripes_xfer(ocm_alloc_t a, bool to_far, const Side &local, uint64_t 
     Ctx &c = ctx();
     const size_t N = a->stripes.size();
     if (!N || !local.ptr) return OCM_EINVAL;
-    if (local_off + n > local.bytes) return OCM_ERANGE;
+    if (!fits(local, local_off, n)) return OCM_ERANGE;
     if (a->kind == OCM_REPLICATED_GPU) {
-        if (far_off + n > a->stripe_bytes) return OCM_ERANGE;
+        if (n > a->stripe_bytes || far_off > a->stripe_bytes - n) return OCM_ERANGE;
         if (!to_far) {
             const Side &near = a->stripes[(size_t)c.rank < N ? (size_t)c.rank : 0];
             return side_copy(local, local_off, nullptr, 0, near, far_off, n, nullptr, stream, used);
@@ -337,7 +347,7 @@ static int stripes_xfer(ocm_alloc_t a, bool to_far, const Side &local, uint64_t 
         return OCM_OK;
     }
     // striped
-    if (far_off + n > a->stripe_bytes * N) return OCM_ERANGE;
+    if (n > a->stripe_bytes * N || far_off > a->stripe_bytes * N - n) return OCM_ERANGE;
     while (n) {
         const size_t r = (size_t)(far_off / a->stripe_bytes);
         const uint64_t in = far_off % a->stripe_bytes;
@@ -434,14 +444,45 @@ static int do_onesided(ocm_alloc_t a, const struct ocm_params *p, void *stream, 
     return err;
 }
 
+// The calling thread's completion slot (Ctx::done_word): claimed on first use, returned when the thread exits.
+struct DoneSlot {
+    int slot = -1;
+    uint64_t *epoch = nullptr;      // the done_word array the slot belongs to (a re-init after ocm_tini makes a new one)
+    ~DoneSlot() { release(); }
+    void release() {
+        Ctx &c = ctx();
+        if (slot >= 0 && epoch && epoch == c.done_word) c.done_slots_free.fetch_or(1ull << slot, std::memory_order_release);
+        slot = -1;
+        epoch = nullptr;
+    }
+    int get() {
+        Ctx &c = ctx();
+        if (slot >= 0 && epoch == c.done_word) return slot;
+        slot = -1;
+        uint64_t fr = c.done_slots_free.load(std::memory_order_acquire);
+        while (fr) {
+            const int s = __builtin_ctzll(fr);
+            if (c.done_slots_free.compare_exchange_weak(fr, fr & ~(1ull << s), std::memory_order_acq_rel)) {
+                slot = s;
+                epoch = c.done_word;
+                break;
+            }
+        }
+        return slot;   // -1: more than kDoneSlots threads are blocking at once; this one synchronises its stream
+    }
+};
+static thread_local DoneSlot t_done_slot;
+
 // Arm the completion word for the blocking call that follows on this thread.
 static void arm_sync_notify() {
     Ctx &c = ctx();
     t_sn = SyncNotify();
     if (!c.done_word || c.device < 0) return;
+    const int s = t_done_slot.get();
+    if (s < 0) return;
     t_sn.armed = true;
-    t_sn.value = c.done_seq.fetch_add(1, std::memory_order_relaxed) + 1;
-    t_sn.cn.flag = c.done_word;
+    t_sn.value = ++c.done_seq[s];
+    t_sn.cn.flag = c.done_word + (size_t)s * kDoneSlotWords;
     t_sn.cn.value = t_sn.value;
 }
 
@@ -451,7 +492,7 @@ static int finish_sync(int err, bool used, void *stream) {
         bool done = false;
         if (!err && !stream && t_sn.armed && t_sn.gpu_ops == 1 && t_sn.notified == 1) {
             // exactly one kernel: wait for its completion word (bounded, then fall back to the stream)
-            volatile uint64_t *w = c.done_word;
+            volatile uint64_t *w = t_sn.cn.flag;   // this thread's own slot: only its kernels write it, in order
             struct timespec t0, t1;
             clock_gettime(CLOCK_MONOTONIC, &t0);
             for (unsigned spin = 0; !done; ++spin) {
@@ -572,6 +613,11 @@ int ocm_copy_in(ocm_alloc_t dst, void *src) {
         set_last_error(OCM_EINVAL);
         return -1;
     }
+    if (stale(dst)) {   // an attached handle whose owner has freed (and maybe recycled) the block
+        set_last_error(OCM_ESTALE);
+        return -1;
+    }
+    arm_sync_notify();
     bool used = false;
     int err;
     const Side *far = far_side(dst);
@@ -596,6 +642,11 @@ int ocm_copy_out(void *dstp, ocm_alloc_t src) {
         set_last_error(OCM_EINVAL);
         return -1;
     }
+    if (stale(src)) {
+        set_last_error(OCM_ESTALE);
+        return -1;
+    }
+    arm_sync_notify();
     bool used = false;
     int err;
     const Side *far = far_side(src);

@@ -115,11 +115,16 @@ struct Ctx {
     std::atomic<uint32_t> ticket_cursor{0};
     // counters
     std::atomic<uint64_t> n_alloc{0}, n_free{0}, n_fast{0}, n_slow{0}, n_copies{0}, copy_bytes{0};
-    unsigned long long kernel_launches = 0;
+    std::atomic<unsigned long long> kernel_launches{0};
     std::atomic<uint64_t> bytes_live[TIER_COUNT];
     PeerExec     peer_exec[kMaxGpus];
-    uint64_t    *done_word = nullptr;   // pinned, device-visible: kernels of blocking calls report completion here
-    std::atomic<uint64_t> done_seq{0};
+    // Completion words of blocking calls: pinned, device-visible, one 64-byte slot per calling thread (a thread
+    // claims a slot for its lifetime).  The kernel of a blocking call stores that thread's next sequence number
+    // into the thread's own slot, so one thread's kernel can never satisfy another thread's wait and a slot only
+    // ever counts upwards (kernels of one thread run in launch order on the library stream).
+    uint64_t    *done_word = nullptr;          // kDoneSlots slots of 8 words each
+    std::atomic<uint64_t> done_slots_free{0};  // bit s set: slot s is free
+    uint64_t     done_seq[64] = {0};           // last sequence number handed out per slot (owner thread only)
     gpu::McObject mc;            // rank 0's multicast object mapped for our device
     bool         mc_tried = false;
     // Puts at least this large are pulled by the owner GPU (0: never, the default).  Measured on 2xB200:
@@ -130,6 +135,8 @@ struct Ctx {
     std::atomic<uint64_t> n_pulled{0};
 };
 constexpr int kNumTickets = 1024;
+constexpr int kDoneSlots = 64;
+constexpr int kDoneSlotWords = 8;
 
 Ctx &ctx();
 void set_last_error(int e);

@@ -10,6 +10,7 @@
 #include <cstring>
 #include <cuda_runtime.h>
 #include <mutex>
+#include <vector>
 
 using namespace ocm;
 
@@ -22,6 +23,7 @@ struct DevScratch {
     std::atomic<uint32_t> cursor{0};
     void  *sort_scratch = nullptr;
     size_t sort_bytes = 0;
+    std::vector<void *> retired;   // outgrown sort scratch buffers (at most log2 of them; freed with the context)
 };
 DevScratch g_dev[64];
 std::mutex g_dev_mu;
@@ -65,7 +67,9 @@ ocmk::StridedDesc to_desc(const struct ocmk_strided *d) {
 
 extern "C" {
 
-uint64_t ocmk_launch_count(void) { return g_abi_launches.load() + ctx().kernel_launches; }
+uint64_t ocmk_launch_count(void) {
+    return g_abi_launches.load() + ctx().kernel_launches.load() + ocmk::extra_launches().load();
+}
 
 int ocmk_copy(void *dst, void *dst2, const void *src, size_t bytes, uint64_t *signal, void *stream) {
     unsigned long long n = 0;
@@ -139,24 +143,30 @@ int ocmk_sort_u64(uint64_t *keys, uint64_t *tmp, uint64_t n, void *stream) {
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return -OCM_ENOGPU;
     DevScratch &d = g_dev[dev];
     size_t need = ocmk::sort_scratch_bytes(n);
+    void *scratch = nullptr;
+    size_t scratch_bytes = 0;
     {
+        // One scratch buffer per device, grown on demand and shared by every call on that device: sorts whose
+        // kernels overlap on one GPU (other streams, other threads) race on it - serialise them, like the
+        // allocation-free variant.  An outgrown buffer is parked, not freed: a sort launched earlier on another
+        // stream may still be using it.
         std::lock_guard<std::mutex> g(g_dev_mu);
         if (d.sort_bytes < need) {
-            if (d.sort_scratch) {
-                cudaDeviceSynchronize();
-                cudaFree(d.sort_scratch);
-                d.sort_scratch = nullptr;
-                d.sort_bytes = 0;
-            }
-            if (cudaMalloc(&d.sort_scratch, need) != cudaSuccess) {
+            void *p = nullptr;
+            need = (need + (1u << 20) - 1) & ~(size_t)((1u << 20) - 1);
+            if (cudaMalloc(&p, need) != cudaSuccess) {
                 cudaGetLastError();
                 return -OCM_ENOMEM;
             }
+            if (d.sort_scratch) d.retired.push_back(d.sort_scratch);
+            d.sort_scratch = p;
             d.sort_bytes = need;
         }
+        scratch = d.sort_scratch;
+        scratch_bytes = d.sort_bytes;
     }
     unsigned long long nl = 0;
-    cudaError_t e = ocmk::launch_sort_u64(keys, tmp, n, d.sort_scratch, d.sort_bytes, (cudaStream_t)stream, &nl);
+    cudaError_t e = ocmk::launch_sort_u64(keys, tmp, n, scratch, scratch_bytes, (cudaStream_t)stream, &nl);
     g_abi_launches += nl;
     return ret(e, "ocmk_sort_u64");
 }
@@ -208,8 +218,9 @@ static int strided_sides(const Side &dst, const Side &src, const struct ocm_stri
     cudaStream_t st = (cudaStream_t)(stream ? stream : c.stream);
     c.n_copies.fetch_add(1, std::memory_order_relaxed);
     c.copy_bytes.fetch_add(d->extent[0] * n[0] * n[1] * n[2], std::memory_order_relaxed);
-    cudaError_t e = ocmk::launch_strided(k, sig ? sig->gpu_signal() : nullptr, next_ticket(), st,
-                                         &c.kernel_launches);
+    unsigned long long nl = 0;
+    cudaError_t e = ocmk::launch_strided(k, sig ? sig->gpu_signal() : nullptr, next_ticket(), st, &nl);
+    c.kernel_launches.fetch_add(nl, std::memory_order_relaxed);
     if (e == cudaSuccess) return OCM_OK;
     LOGE("strided kernel: %s", cudaGetErrorString(e));
     cudaGetLastError();

@@ -4,7 +4,10 @@
  * The reference keeps a global list without covering every access and documents no threading contract
  * (reference src/lib.c:81-93); here the contract is in INTEGRATION.md ("Threading") and this program holds it to it.
  *
- *   ocm_mt [threads=8] [iterations=200]
+ *   ocm_mt [threads=8] [iterations=200] [gpu]
+ * With "gpu" the pairs are OCM_REMOTE_GPU: every blocking copy is then one kernel whose completion the caller
+ * waits for on its own completion word, and the bytes are read back and checked right after each call - a thread
+ * that returned early because ANOTHER thread's kernel finished would see stale data here.
  */
 #include <oncillamem.h>
 #include <pthread.h>
@@ -13,6 +16,7 @@
 #include <string.h>
 
 static int g_iters = 200;
+static int g_gpu = 0;
 static int g_fail = 0;
 static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
 /* one shared block all threads put into: its signal must count every copy exactly once */
@@ -49,7 +53,7 @@ static void *worker(void *arg) {
         size_t len = 0, i;
         const unsigned char tag = (unsigned char)(id * 16 + it);
         memset(&ap, 0, sizeof ap);
-        ap.base.kind = OCM_REMOTE_HOST;
+        ap.base.kind = g_gpu ? OCM_REMOTE_GPU : OCM_REMOTE_HOST;
         ap.base.local_alloc_bytes = bytes;
         ap.base.rem_alloc_bytes = bytes;
         ap.policy = (it % 3 == 0) ? OCM_POLICY_ROUND_ROBIN : OCM_POLICY_DEFAULT;
@@ -70,7 +74,7 @@ static void *worker(void *arg) {
         ocm_localbuf(host, &p, &len);
         h = p;
         for (i = 0; i < bytes; ++i) {
-            if (w[i] != 0) {
+            if (!g_gpu && w[i] != 0) {
                 FAIL("thread %d it %d: window not zeroed at %zu", id, it, i);
                 break;
             }
@@ -80,10 +84,16 @@ static void *worker(void *arg) {
         cp.bytes = bytes;
         cp.op_flag = 1;
         if (ocm_copy(pair, host, &cp) != 0) FAIL("thread %d it %d: copy host->pair", id, it);   /* host -> window -> far */
-        memset(w, 0, bytes);
+        if (!g_gpu) memset(w, 0, bytes);
         memset(h, 0, bytes);
-        cp.op_flag = 0;
-        if (ocm_copy_onesided(pair, &cp) != 0) FAIL("thread %d it %d: get", id, it);           /* far -> window */
+        if (g_gpu) {
+            /* far -> window -> host allocation, one kernel; the host bytes are checked as soon as the call returns */
+            if (ocm_copy(host, pair, &cp) != 0) FAIL("thread %d it %d: copy pair->host", id, it);
+            w = h;
+        } else {
+            cp.op_flag = 0;
+            if (ocm_copy_onesided(pair, &cp) != 0) FAIL("thread %d it %d: get", id, it);       /* far -> window */
+        }
         for (i = 0; i < bytes; ++i)
             if (w[i] != (unsigned char)(tag + i)) {
                 FAIL("thread %d it %d: byte %zu is %u, want %u", id, it, i, w[i], (unsigned char)(tag + i));
@@ -113,6 +123,7 @@ int main(int argc, char **argv) {
     uint64_t sig = 0;
     int i;
     if (argc > 2) g_iters = atoi(argv[2]);
+    if (argc > 3 && !strcmp(argv[3], "gpu")) g_gpu = 1;
     if (n_threads < 1 || n_threads > 64) return 2;
     if (ocm_init() != 0) {
         printf("FAIL: cannot connect to OCM: %s\n", ocm_strerror(ocm_last_error()));

@@ -21,6 +21,17 @@ def test_reference_arm_prints_one_json_line_and_exits_zero():
     assert "unavailable" in out or out.get("metric", "").startswith("ocm_copy GB/s")
 
 
+def test_both_arms_print_the_same_metric_string():
+    """The driver only computes vs_reference when metric, unit and direction agree: one constant serves both arms."""
+    sys.path.insert(0, str(REPO / "baseline"))
+    import ref_harness
+
+    src = (REPO / "bench.py").read_text()
+    assert "from ref_harness import METRIC" in src and '"metric": METRIC' in src
+    assert '"metric": METRIC' in (REPO / "baseline" / "ref_harness.py").read_text()
+    assert ref_harness.METRIC.startswith("ocm_copy GB/s")
+
+
 def test_bench_defaults_and_flags():
     r = subprocess.run([sys.executable, str(REPO / "bench.py"), "--help"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0
@@ -58,7 +69,8 @@ def test_checkpoint_header_rejects_garbage(tmp_path):
 @pytest.mark.gpu
 def test_bench_json_contract_on_gpu():
     """One short device-timed run: every key the driver reads is present and sane."""
-    r = subprocess.run([sys.executable, str(REPO / "bench.py"), "--steps", "3", "--warmup", "3"], capture_output=True,
+    r = subprocess.run([sys.executable, str(REPO / "bench.py"), "--steps", "3", "--warmup", "3", "--curve-max", str(16 << 20)],
+                       capture_output=True,
                        text=True, timeout=600, cwd=str(REPO))
     assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
     lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
@@ -71,3 +83,10 @@ def test_bench_json_contract_on_gpu():
     assert out["value"] > 100 and out["gpu_launches"] > 0
     assert out["e2e"]["value"] > 1 and out["e2e"]["h2d_bytes_per_step"] > 0 and out["e2e"]["d2h_bytes_per_step"] > 0
     assert {"sm_mhz", "sm_max_mhz", "reasons"} <= set(out["clocks"])
+    sys.path.insert(0, str(REPO / "baseline"))
+    import ref_harness
+
+    assert out["metric"] == ref_harness.METRIC and out["unit"] == "GB/s"
+    assert [r["bytes"] for r in out["curve"]] == [4 << 10, 64 << 10, 1 << 20, 16 << 20]
+    for r in out["curve"]:
+        assert r["put_GBps"] > 0 and r["get_GBps"] > 0 and r["copy_GBps"] > 0

@@ -391,6 +391,15 @@ def test_native_ocm_test_program_gpu(gpu_cluster):
         assert "pass: OCM test completed successfully" in r.stdout
 
 
+def test_blocking_copies_from_many_threads_gpu(gpu_cluster):
+    """eight threads of one process issue blocking GPU copies at once; each waits on its OWN
+    completion slot, so no call may return before its own kernel has run (tests/cpp/ocm_mt.c checks every byte
+    right after each call)."""
+    r = run_app(gpu_cluster, 0, [BIN / "ocm_mt", "8", "150", "gpu"], timeout=300)
+    assert r.returncode == 0 and "pass: ocm_mt 8 threads x 150 iterations" in r.stdout and "FAIL" not in r.stdout, \
+        r.stdout[-2000:] + r.stderr[-2000:]
+
+
 def test_examples_on_gpu(gpu_cluster):
     """examples/: the C hello program with a remote-GPU pair, and a user kernel that works on the far side
     through ocm_remote_ptr()."""

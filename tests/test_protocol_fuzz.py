@@ -100,3 +100,72 @@ def test_garbage_on_tcp_uds_and_mq_does_not_hurt_the_daemons():
         r = run_app(cl, 1, [BIN / "ocm_test", "3", "1", "1", "1"])
         assert r.returncode == 0 and "pass: OCM test completed successfully" in r.stdout, r.stdout + r.stderr
         assert all(p.poll() is None for p in cl.procs.values())
+
+
+def _frame(mtype, payload, status=1, rank=1, seq=77):
+    """A well-formed 192-byte Message (src/common/msg.hpp): header (32 B) + 160-byte union."""
+    hdr = struct.pack("<IHHHHiiIi", 0x4F434D32, 2, mtype, status, 0, os.getpid(), rank, seq, 0)
+    hdr += bytes(32 - len(hdr))
+    return hdr + payload + bytes(160 - len(payload))
+
+
+def _exchange(port, frame, expect_reply=True):
+    s = socket.create_connection(("127.0.0.1", port), timeout=5)
+    s.settimeout(3)
+    s.sendall(frame)
+    data = b""
+    try:
+        while expect_reply and len(data) < 192:
+            chunk = s.recv(192 - len(data))
+            if not chunk:
+                break
+            data += chunk
+    except OSError:
+        pass
+    s.close()
+    return data
+
+
+def test_huge_sizes_and_bad_tiers_on_the_wire_are_refused():
+    """Well-formed frames with sizes near 2^64 and out-of-range tiers: `used + bytes` and
+    `(bytes + granule - 1) / granule` must not wrap, and a wire tier must never index past the cluster table."""
+    MSG_REQ_ALLOC, MSG_DO_ALLOC, MSG_DO_FREE, MSG_NOTE_FREE = 5, 6, 8, 16
+    ALLOC_MEM_REMOTE_HOST, TIER_HOST, OCM_POLICY_DEFAULT = 6, 1, 0
+    with ocm.LocalCluster(2, host_bytes=16 << 20, extra_env={"OCM_NO_GPU": "1"}) as cl:
+        _healthy(cl)
+        p0, p1 = _ports(cl)
+        # something must be reserved first: the wrapping sum is only accepted when used > 0
+        out = run_py(cl, 0, r"""
+import oncilla_b200 as ocm
+ocm.init()
+keep = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 1 << 20)
+for huge in (2**64 - 1, 2**64 - 4096, 2**63, (16 << 20) + 1):
+    for flags in (0, ocm.ALLOC_SLOW_PATH):
+        try:
+            ocm.alloc(ocm.OCM_REMOTE_HOST, 0, huge, flags=flags | ocm.ALLOC_NO_WINDOW)
+            print("ACCEPTED", huge, flags)
+        except ocm.OcmError:
+            pass
+keep.free()
+ocm.tini()
+print("DONE")
+""")
+        assert out.returncode == 0 and "DONE" in out.stdout and "ACCEPTED" not in out.stdout, out.stdout + out.stderr
+        for huge in (2**64 - 1, 2**64 - 4096, 2**63):
+            # placement request straight to rank 0
+            req = struct.pack("<iiQIIII", 1, -1, huge, ALLOC_MEM_REMOTE_HOST, OCM_POLICY_DEFAULT, 0, 0)
+            rep = _exchange(p0, _frame(MSG_REQ_ALLOC, req))
+            assert len(rep) == 192 and struct.unpack_from("<i", rep, 24)[0] != 0, "rank 0 placed a 2^64-byte block"
+            # fulfilment request straight to the owner rank
+            alloc = struct.pack("<iiQIIQQQIIII", 0, 1, 0, ALLOC_MEM_REMOTE_HOST, TIER_HOST, huge, 0, 0, 0, 0, 0, 0)
+            rep = _exchange(p1, _frame(MSG_DO_ALLOC, alloc, rank=0))
+            assert len(rep) == 192 and struct.unpack_from("<i", rep, 24)[0] != 0, "owner carved a 2^64-byte block"
+        for tier in (2, 7, 99, 0xFFFFFFFF):
+            alloc = struct.pack("<iiQIIQQQIIII", 0, 1, 1, ALLOC_MEM_REMOTE_HOST, tier, 4096, 0, 0, 0, 0, 0, 0)
+            _exchange(p0, _frame(MSG_NOTE_FREE, alloc, status=0), expect_reply=False)
+            rep = _exchange(p1, _frame(MSG_DO_FREE, alloc))
+            assert len(rep) == 192 and struct.unpack_from("<i", rep, 24)[0] != 0
+            rep = _exchange(p1, _frame(MSG_DO_ALLOC, alloc))
+            assert len(rep) == 192 and struct.unpack_from("<i", rep, 24)[0] != 0
+        _healthy(cl)
+        assert all(p.poll() is None for p in cl.procs.values())
