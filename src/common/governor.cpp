@@ -27,6 +27,11 @@ int governor_add_node(ClusterTable *c, int rank, const NodeConfig &cfg, const ui
     n.num_gpu = cfg.num_gpu;
     memcpy(n.gpu_mem, cfg.gpu_mem, sizeof n.gpu_mem);
     memcpy(n.ip, cfg.ip, sizeof n.ip);
+    memcpy(n.pci_bdf, cfg.pci_bdf, sizeof n.pci_bdf);
+    n.pci_bdf[sizeof n.pci_bdf - 1] = 0;
+    n.numa_node = cfg.numa_node;
+    n.peer_mask = cfg.peer_mask;
+    n.caps = cfg.caps;
     for (int t = 0; t < TIER_COUNT; ++t) n.pool_bytes[t] = pool_bytes[t];
     if (!rejoin) {
         for (int t = 0; t < TIER_COUNT; ++t) n.used[t].store(0, std::memory_order_relaxed);
@@ -56,14 +61,28 @@ bool governor_rank_alive(const ClusterTable *c, int rank) {
     return now < beat || now - beat < kRankDeadAfterNs;
 }
 
-static bool try_rank(ClusterTable *c, int rank, Tier want, uint64_t bytes, Tier *got, bool *dead) {
+bool governor_gpu_reachable(const ClusterTable *c, int from_rank, int to_rank) {
+    if (from_rank < 0 || from_rank >= c->n_ranks || to_rank < 0 || to_rank >= c->n_ranks) return false;
+    const NodeSlot &f = c->node[from_rank], &t = c->node[to_rank];
+    if (t.gpu_index < 0) return false;
+    if (from_rank == to_rank || f.gpu_index == t.gpu_index) return true;
+    // a requester without a GPU of its own, or one that reported no peer row (older daemon, unit tests): not known
+    // to be unreachable - the mapping step decides, as before
+    if (f.gpu_index < 0 || f.peer_mask == 0) return true;
+    return t.gpu_index < 32 && (f.peer_mask >> t.gpu_index) & 1u;
+}
+
+static bool try_rank(ClusterTable *c, int orig, int rank, Tier want, uint64_t bytes, Tier *got, bool *dead) {
     if (rank < 0 || rank >= c->n_ranks) return false;
     if (!c->node[rank].joined.load(std::memory_order_acquire)) return false;
     if (!governor_rank_alive(c, rank)) {   // its daemon stopped beating: place elsewhere (the reference hangs here)
         *dead = true;
         return false;
     }
-    if (c->node[rank].pool_bytes[want] && cluster_reserve(c, rank, want, bytes)) {
+    // HBM the requester's GPU cannot load from / store to is no use to it: down-tier to that rank's pinned host
+    // pool (below) instead of failing later, when the application tries to map the pool
+    const bool gpu_ok = want != TIER_GPU || governor_gpu_reachable(c, orig, rank);
+    if (gpu_ok && c->node[rank].pool_bytes[want] && cluster_reserve(c, rank, want, bytes)) {
         *got = want;
         return true;
     }
@@ -125,7 +144,7 @@ int governor_place(ClusterTable *c, const AllocRequest &req, Allocation *out) {
     bool dead = false;
     for (int i = 0; i < n; ++i) {
         Tier got;
-        if (!try_rank(c, order[i], want, req.bytes, &got, &dead)) continue;
+        if (!try_rank(c, req.orig_rank, order[i], want, req.bytes, &got, &dead)) continue;
         memset(out, 0, sizeof *out);
         out->orig_rank = req.orig_rank;
         out->remote_rank = order[i];

@@ -43,4 +43,8 @@ int governor_joined(const ClusterTable *c);
 // failure detection at all: a request for a dead node blocks in connect() or forever.
 bool governor_rank_alive(const ClusterTable *c, int rank);
 
+// Can the GPU of `from_rank` address the HBM pool of `to_rank` directly (same GPU, or a peer its daemon found with
+// cudaDeviceCanAccessPeer at start-up)?  governor_place gives unreachable candidates the host tier instead.
+bool governor_gpu_reachable(const ClusterTable *c, int from_rank, int to_rank);
+
 } // namespace ocm

@@ -10,7 +10,7 @@
 namespace ocm {
 
 constexpr uint32_t kMsgMagic   = 0x4F434D32u; // "OCM2"
-constexpr uint16_t kMsgVersion = 2;
+constexpr uint16_t kMsgVersion = 3;
 constexpr int      kMaxRanks   = 64;
 constexpr int      kMaxGpus    = 8;   // reference inc/alloc.h:30
 
@@ -77,14 +77,20 @@ struct Allocation {
     uint32_t pad;
 };
 
+enum NodeCaps : uint8_t { NODE_CAP_MULTICAST = 1, NODE_CAP_VMM_FD = 2 };
 struct NodeConfig {
-    char     ip[64];        // ib_ip in the reference (inc/alloc.h:59)
+    char     ip[48];        // ib_ip in the reference (inc/alloc.h:59)
+    char     pci_bdf[16];   // PCI address of the rank's GPU ("0000:1b:00.0"), empty without one
     uint64_t ram;           // pinned-host pool bytes
     uint64_t gpu_mem[kMaxGpus];
     int32_t  num_gpu;
     int32_t  gpu_index;     // CUDA ordinal backing this rank, -1 if none
     int32_t  daemon_pid;
-    int32_t  pad;
+    // topology of the rank's GPU (common/topo.hpp): host NUMA node (-1 unknown), the CUDA ordinals it reaches
+    // directly (bit per ordinal, kMaxGpus = 8), NodeCaps
+    int16_t  numa_node;
+    uint8_t  peer_mask;
+    uint8_t  caps;
 };
 
 struct StatsPayload {

@@ -76,6 +76,12 @@ bool parse_nodefile_text(const std::string &text, Nodefile *out, std::string *er
             if (k == "gpu") e.gpu = (int)strtol(v.c_str(), nullptr, 10);
             else if (k == "gpu_bytes") ok = parse_size(v.c_str(), &e.gpu_bytes);
             else if (k == "host_bytes") ok = parse_size(v.c_str(), &e.host_bytes);
+            else if (k == "numa") {
+                char *ve = nullptr;
+                long nn = strtol(v.c_str(), &ve, 10);
+                ok = ve != v.c_str() && !*ve && nn >= -1 && nn < 1024;
+                if (ok) e.numa = (int)nn;
+            }
             else ok = false;
             if (!ok) {
                 if (err) *err = "line " + std::to_string(lineno) + ": bad option `" + tok[i] + "`";

@@ -2,7 +2,7 @@
 // Accepts the reference's format `rank dns ethernet_ip ocm_port rdmacm_port`
 // with `#` comments (reference src/nodefile.c:30-37, bin/nodefile.rdma:1-3; the
 // .rma variant without the last column, bin/nodefile.rma:1-3) and optional
-// trailing key=value columns: gpu=<ordinal> gpu_bytes=<n[KMGT]> host_bytes=<n[KMGT]>.
+// trailing key=value columns: gpu=<ordinal> gpu_bytes=<n[KMGT]> host_bytes=<n[KMGT]> numa=<node>.
 // Rank discovery: OCM_RANK overrides; otherwise the hostname match of the
 // reference (src/nodefile.c:92-103); a one-line file is rank 0.
 #pragma once
@@ -21,6 +21,7 @@ struct NodeEntry {
     int         gpu = -2;            // -2: choose rank % device_count, -1: no GPU
     uint64_t    gpu_bytes = 0;       // 0: default
     uint64_t    host_bytes = 0;      // 0: default
+    int         numa = -2;           // host NUMA node of the rank's pinned pool; -2: the node of its GPU (sysfs), -1: do not bind
 };
 
 struct Nodefile {

@@ -34,7 +34,7 @@
 namespace ocm {
 
 constexpr uint64_t kTableMagic   = 0x4F434D5441424C45ull; // "OCMTABLE"
-constexpr uint32_t kTableVersion = 6;
+constexpr uint32_t kTableVersion = 7;
 constexpr uint32_t kMaxGranules  = 1u << 18;
 constexpr uint64_t kMcGranule     = 64ull << 10;
 constexpr uint32_t kMcMaxGranules = 1u << 14;     // multicast region <= 1 GiB
@@ -127,7 +127,15 @@ struct NodeSlot {
     std::atomic<uint64_t> used[TIER_COUNT];   // reserved bytes, rank-0 capacity accounting
     std::atomic<uint64_t> live;
     uint64_t gpu_mem[kMaxGpus];
-    char     ip[64];
+    char     ip[48];
+    // Topology reported at join (common/topo.hpp): PCI address and host NUMA node of the rank's GPU (-1: the
+    // kernel does not know, e.g. inside a VM), which CUDA ordinals that GPU reaches directly, NodeCaps bits.
+    // governor_place keeps HBM far sides off GPUs the requester's GPU cannot reach.
+    char     pci_bdf[16];
+    int32_t  numa_node;
+    uint32_t peer_mask;
+    uint32_t caps;
+    uint32_t pad_topo;
     // Liveness: the rank's daemon stores CLOCK_MONOTONIC here on every timer tick (20 ms).  0 = has not
     // beaten yet (just joined, or a table without daemons in the unit tests) and counts as alive.
     std::atomic<uint64_t> heartbeat_ns;

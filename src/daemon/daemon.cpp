@@ -95,13 +95,34 @@ int Daemon::setup_pools() {
         if (!gpu_bytes) {
             size_t fr = 0, tot = 0;
             gpu::mem_info(gpu_, &fr, &tot);
-            gpu_bytes = std::min<uint64_t>(16ull << 30, fr / 2);
+            // default: most of the free HBM (a B200 has ~178 GiB free: 160 GiB pooled), leaving room for the contexts
+            // and working memory of the applications that share the GPU.  OCM_GPU_BYTES / nodefile gpu_bytes= override.
+            // Ranks that share one GPU (more nodefile lines than devices) split it evenly.
+            int sharers = 0;
+            for (int r = 0; r < n_ranks_; ++r) {
+                const int g = nf_.nodes[r].gpu >= 0 ? nf_.nodes[r].gpu : nf_.nodes[r].gpu == -1 ? -1 : r % ndev;
+                sharers += g == gpu_;
+            }
+            if (sharers < 1) sharers = 1;
+            gpu_bytes = fr > (24ull << 30) ? fr - std::max<uint64_t>(fr / 10, 16ull << 30) : fr / 2;
+            gpu_bytes /= (uint64_t)sharers;
         }
     } else {
         gpu_bytes = 0;
     }
 
     std::string err;
+    // Topology of our GPU: which peers it reaches, multicast, and the host NUMA node it hangs off.  The pinned host
+    // pool is first-touched and bound there (nodefile `numa=<n>` overrides, `numa=-1` disables), and the daemon's
+    // threads run on that node's CPUs, so the GPU's PCIe reads of the pool stay on one socket.
+    if (gpu_ >= 0) topo::discover_gpu(gpu_, &topo_);
+    host_numa_ = me.numa >= -1 ? me.numa : topo_.numa_node;
+    if (host_numa_ >= 0 && topo::numa_nodes().size() > 1) {
+        if (topo::bind_thread_to_node(host_numa_)) LOGI("daemon threads bound to NUMA node %d", host_numa_);
+        else LOGW("cannot bind to NUMA node %d (no such node or not permitted)", host_numa_);
+    } else if (host_numa_ >= 0 && topo::node_cpus(host_numa_).empty()) {
+        host_numa_ = -1;
+    }
     // GPU pool first: VMM rounds the size up, the table must describe the real size.
     uint8_t ipc_handle[64] = {0};
     if (gpu_ >= 0 && gpu_bytes) {
@@ -154,7 +175,10 @@ int Daemon::setup_pools() {
             LOGE("%s", err.c_str());
             return -ENOMEM;
         }
-        // touch + pin so that the pool is resident and device-visible
+        // place (NUMA node of the GPU), touch + pin so that the pool is resident and device-visible
+        if (host_numa_ >= 0 && !topo::prefer_node_for_range(host_map_.base, host_map_.bytes, host_numa_))
+            LOGD("mbind refused: relying on first touch from threads bound to node %d", host_numa_);
+        topo::touch_range(host_map_.base, host_map_.bytes, host_numa_, 8);
         if (gpu_ >= 0 && !gpu::host_register(host_map_.base, host_map_.bytes, &err))
             LOGW("host pool not pinned: %s", err.c_str());
     }
@@ -282,6 +306,10 @@ void Daemon::join_cluster() {
     c.num_gpu = gpu::device_count();
     c.gpu_index = gpu_;
     c.daemon_pid = (int)getpid();
+    snprintf(c.pci_bdf, sizeof c.pci_bdf, "%s", topo_.pci_bdf);
+    c.numa_node = (int16_t)host_numa_;
+    c.peer_mask = (uint8_t)(topo_.peer_mask & 0xffu);
+    c.caps = (uint8_t)((topo_.multicast ? NODE_CAP_MULTICAST : 0) | (topo_.vmm_fd_export ? NODE_CAP_VMM_FD : 0));
     for (int d = 0; d < c.num_gpu && d < kMaxGpus; ++d) {
         size_t fr = 0, tot = 0;
         if (d == gpu_ && gpu::mem_info(d, &fr, &tot)) c.gpu_mem[d] = tot;

@@ -20,6 +20,7 @@
 #include "../common/nodefile.hpp"
 #include "../common/ring.hpp"
 #include "../common/tables.hpp"
+#include "../common/topo.hpp"
 #include "../ipc/pmsg.hpp"
 #include <atomic>
 #include <map>
@@ -93,6 +94,8 @@ class Daemon {
     Nodefile nf_;
     int rank_ = -1, n_ranks_ = 0;
     int gpu_ = -1;
+    topo::GpuTopo topo_;                    // what the runtime and sysfs know about gpu_ (peer row, NUMA node, ...)
+    int host_numa_ = -1;                    // NUMA node the pinned host pool is bound to (-1: not bound)
     ShmMapping tbl_map_, host_map_, cluster_map_;
     TableHeader *tbl_ = nullptr;
     ClusterTable *cluster_ = nullptr;       // rank 0 only (owner)

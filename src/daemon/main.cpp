@@ -2,7 +2,9 @@
 // Usage mirrors the reference (`bin/oncillamem <nodefile>`, reference
 // src/main.c:162-166,187-224) with optional overrides.
 #include "daemon.hpp"
+#include "../common/gpu_rt.hpp"
 #include "../common/log.hpp"
+#include "../common/topo.hpp"
 #include <csignal>
 #include <cstdio>
 #include <cstring>
@@ -13,7 +15,7 @@ static void usage(const char *argv0) {
     fprintf(stderr,
             "Usage: %s <nodefile> [--rank N] [--gpu-bytes SIZE] [--host-bytes SIZE] [--no-gpu] [--join-timeout MS] [--check]\n"
             "  --check: parse the nodefile, print the topology and this process's rank, then exit\n"
-            "  nodefile lines: rank dns ethernet_ip ocm_port [rdmacm_port] [gpu=<i>] [gpu_bytes=<n>] [host_bytes=<n>]\n"
+            "  nodefile lines: rank dns ethernet_ip ocm_port [rdmacm_port] [gpu=<i>] [gpu_bytes=<n>] [host_bytes=<n>] [numa=<node>]\n"
             "  environment: OCM_RANK, OCM_NS, OCM_GPU_BYTES, OCM_HOST_BYTES, OCM_LOG|OCM_VERBOSE, OCM_NO_SCRUB, OCM_GPU_IPC\n",
             argv0);
 }
@@ -36,6 +38,24 @@ static int check_nodefile(const ocm::DaemonOptions &o) {
         else snprintf(gpu, sizeof gpu, "%d", n.gpu);
         printf("%4d  %-20s %-15s %6d  %-5s %12llu %12llu\n", n.rank, n.dns.c_str(), n.ip_eth.c_str(), n.ocm_port, gpu,
                (unsigned long long)n.gpu_bytes, (unsigned long long)n.host_bytes);
+    }
+    // what this machine offers: host NUMA nodes, and per GPU its PCI address, NUMA node and peer-access row
+    auto nodes = ocm::topo::numa_nodes();
+    printf("host NUMA nodes:");
+    for (int n : nodes) printf(" %d(%zu cpus)", n, ocm::topo::node_cpus(n).size());
+    printf("\n");
+    const int ndev = o.no_gpu ? 0 : ocm::gpu::device_count();
+    if (ndev > 0) {
+        printf("%4s  %-13s %5s %5s %6s  peer access (P = direct load/store, . = none)\n", "gpu", "pci", "numa", "nvls", "vmmfd");
+        for (int d = 0; d < ndev; ++d) {
+            ocm::topo::GpuTopo t;
+            if (!ocm::topo::discover_gpu(d, &t)) continue;
+            printf("%4d  %-13s %5d %5s %6s  ", d, t.pci_bdf, t.numa_node, t.multicast ? "yes" : "no", t.vmm_fd_export ? "yes" : "no");
+            for (int p = 0; p < ndev; ++p) printf("%c", p == d ? 'X' : (t.peer_mask >> p) & 1u ? 'P' : '.');
+            printf("\n");
+        }
+    } else {
+        printf("no CUDA device visible: host tier only\n");
     }
     return nf.my_rank < 0 ? 1 : 0;
 }

@@ -1,5 +1,5 @@
 // Native unit tests of the host substrate (no daemon, no GPU needed):
-//   unit_host <suite>|all     suites: msg nodefile ring tables tables_mt governor pmsg sock oracle
+//   unit_host <suite>|all     suites: msg nodefile ring tables tables_mt governor topo pmsg sock oracle
 // The reference has no unit layer at all; these are new.
 #include "common/governor.hpp"
 #include "common/msg.hpp"
@@ -7,6 +7,9 @@
 #include "common/nodefile.hpp"
 #include "common/ring.hpp"
 #include "common/tables.hpp"
+#include "common/topo.hpp"
+#include <fstream>
+#include <sys/stat.h>
 #include "ipc/pmsg.hpp"
 #include "ipc/sock.hpp"
 #include "oracle/oracle.hpp"
@@ -85,6 +88,15 @@ static void t_nodefile() {
     CHECK(parse_size("1.5G", &v) && v == (3ull << 29));
     CHECK(parse_size("64KiB", &v) && v == 65536);
     CHECK(!parse_size("abc", &v));
+}
+
+static void t_nodefile_numa() {
+    Nodefile nf;
+    std::string err;
+    CHECK(parse_nodefile_text("0 a 127.0.0.1 9000 gpu=0 numa=1\n1 b 127.0.0.1 9001 numa=-1\n2 c 127.0.0.1 9002\n", &nf, &err));
+    CHECK(nf.nodes[0].numa == 1 && nf.nodes[1].numa == -1 && nf.nodes[2].numa == -2);
+    CHECK(!parse_nodefile_text("0 a 127.0.0.1 9000 numa=x\n", &nf, &err));
+    CHECK(!parse_nodefile_text("0 a 127.0.0.1 9000 numa=-7\n", &nf, &err));
 }
 
 static void t_ring() {
@@ -366,6 +378,73 @@ static void t_governor() {
     CHECK(c->mc_owner[3].load() == 0);
 }
 
+// Topology discovery (common/topo.hpp): list parsing, sysfs lookup on a fake tree, binding helpers, and the
+// placement rule built on the peer rows the daemons report.
+static void t_topo() {
+    using namespace ocm::topo;
+    CHECK((parse_cpulist("0-3,8,10-11\n") == std::vector<int>{0, 1, 2, 3, 8, 10, 11}));
+    CHECK(parse_cpulist("").empty() && parse_cpulist("garbage").empty());
+    CHECK((parse_cpulist("5") == std::vector<int>{5}) && (parse_cpulist("7-") == std::vector<int>{7}));
+    std::vector<int> nodes = numa_nodes();
+    CHECK(!nodes.empty());
+    // a fake sysfs with two GPUs on different nodes; the CUDA spelling of the address (8-digit domain, upper case) resolves too
+    char tmpl[] = "/tmp/ocm_topo_XXXXXX";
+    std::string root = mkdtemp(tmpl);
+    for (auto kv : {std::pair<const char *, const char *>{"0000:1b:00.0", "0"}, {"0000:9c:00.0", "1"}, {"0000:aa:00.0", "-1"}}) {
+        std::string d = root + "/bus/pci/devices/" + kv.first;
+        std::string cmd = "mkdir -p " + d;
+        CHECK(system(cmd.c_str()) == 0);
+        std::ofstream(d + "/numa_node") << kv.second << "\n";
+    }
+    CHECK(pci_numa_node("0000:1b:00.0", root) == 0);
+    CHECK(pci_numa_node("00000000:9C:00.0", root) == 1);
+    CHECK(pci_numa_node("0000:aa:00.0", root) == -1);
+    CHECK(pci_numa_node("0000:ff:00.0", root) == -1);
+    std::string rm = "rm -rf " + root;
+    CHECK(system(rm.c_str()) == 0);
+    // binding: unknown nodes are refused, the first real node works and leaves us with a non-empty CPU set
+    CHECK(!bind_thread_to_node(-1) && !bind_thread_to_node(100000));
+    std::thread([&] { CHECK(bind_thread_to_node(nodes[0]) || node_cpus(nodes[0]).empty()); }).join();
+    std::vector<char> page(1 << 16, 7);
+    touch_range(page.data(), page.size(), nodes[0], 3);
+    CHECK(page[0] == 7 && page[page.size() - 1] == 7);   // placement touches never change the content
+    prefer_node_for_range(page.data(), 0, 0);            // degenerate arguments are refused, not crashed on
+
+    // placement: a far side in HBM only on GPUs the requester's GPU reaches; otherwise that rank's host tier
+    std::vector<char> buf(sizeof(ClusterTable), 0);
+    auto *c = reinterpret_cast<ClusterTable *>(buf.data());
+    cluster_format(c, 3);
+    uint64_t pools[TIER_COUNT] = {1ull << 30, 1ull << 28};
+    NodeConfig cfg;
+    for (int r = 0; r < 3; ++r) {
+        memset(&cfg, 0, sizeof cfg);
+        cfg.gpu_index = r;
+        cfg.numa_node = (int16_t)(r / 2);
+        cfg.peer_mask = r == 2 ? 0x4 : 0x3;      // GPUs 0 and 1 see each other; GPU 2 is an island
+        cfg.caps = NODE_CAP_VMM_FD;
+        snprintf(cfg.pci_bdf, sizeof cfg.pci_bdf, "0000:%02x:00.0", 0x1b + r);
+        CHECK(governor_add_node(c, r, cfg, pools) == OCM_OK);
+    }
+    CHECK(c->node[1].numa_node == 0 && c->node[2].numa_node == 1 && c->node[2].peer_mask == 0x4 &&
+          !strcmp(c->node[1].pci_bdf, "0000:1c:00.0"));
+    CHECK(governor_gpu_reachable(c, 0, 1) && governor_gpu_reachable(c, 1, 0) && governor_gpu_reachable(c, 2, 2));
+    CHECK(!governor_gpu_reachable(c, 0, 2) && !governor_gpu_reachable(c, 2, 0) && !governor_gpu_reachable(c, 0, 7));
+    AllocRequest rq;
+    memset(&rq, 0, sizeof rq);
+    Allocation a;
+    rq.bytes = 1 << 20; rq.type = ALLOC_MEM_REMOTE_GPU; rq.policy = OCM_POLICY_DEFAULT;
+    rq.orig_rank = 0;
+    CHECK(governor_place(c, rq, &a) == OCM_OK && a.remote_rank == 1 && a.tier == TIER_GPU);
+    rq.orig_rank = 1;    // the neighbour is the island: its pinned host pool is what rank 1 can use there
+    CHECK(governor_place(c, rq, &a) == OCM_OK && a.remote_rank == 2 && a.tier == TIER_HOST && a.type == ALLOC_MEM_REMOTE_HOST);
+    rq.policy = OCM_POLICY_EXPLICIT; rq.remote_rank = 2; rq.orig_rank = 2;
+    CHECK(governor_place(c, rq, &a) == OCM_OK && a.tier == TIER_GPU);   // its own GPU is always reachable
+    // daemons that report no peer row (peer_mask 0) keep the old behaviour: decided when the pool is mapped
+    c->node[1].peer_mask = 0;
+    rq.policy = OCM_POLICY_DEFAULT; rq.orig_rank = 1;
+    CHECK(governor_place(c, rq, &a) == OCM_OK && a.remote_rank == 2 && a.tier == TIER_GPU);
+}
+
 static void t_pmsg() {
     // equivalent of the reference's pmsg_daemon / pmsg_client pair (test/pmsg_daemon.c, test/pmsg_client.c)
     setenv("OCM_NS", ("ut" + std::to_string(getpid())).c_str(), 1);
@@ -531,8 +610,8 @@ static void t_oracle() {
 int main(int argc, char **argv) {
     std::string which = argc > 1 ? argv[1] : "all";
     std::map<std::string, void (*)()> suites = {
-        {"msg", t_msg}, {"nodefile", t_nodefile}, {"ring", t_ring}, {"tables", t_tables}, {"tables_mt", t_tables_mt},
-        {"governor", t_governor}, {"pmsg", t_pmsg}, {"sock", t_sock}, {"oracle", t_oracle}};
+        {"msg", t_msg}, {"nodefile", t_nodefile}, {"nodefile_numa", t_nodefile_numa}, {"ring", t_ring}, {"tables", t_tables}, {"tables_mt", t_tables_mt},
+        {"governor", t_governor}, {"topo", t_topo}, {"pmsg", t_pmsg}, {"sock", t_sock}, {"oracle", t_oracle}};
     int ran = 0;
     for (auto &kv : suites) {
         if (which != "all" && which != kv.first) continue;

@@ -9,7 +9,7 @@ import pytest
 
 from conftest import BIN
 
-SUITES = ["msg", "nodefile", "ring", "tables", "tables_mt", "governor", "pmsg", "sock", "oracle"]
+SUITES = ["msg", "nodefile", "ring", "tables", "tables_mt", "governor", "topo", "nodefile_numa", "pmsg", "sock", "oracle"]
 
 
 def test_daemon_check_mode(tmp_path):
@@ -23,7 +23,7 @@ def test_daemon_check_mode(tmp_path):
     r = subprocess.run([str(BIN / "oncillamem"), str(REPO / "examples" / "nodefile.8gpu"), "--check"], env=env,
                        capture_output=True, text=True, timeout=30)
     assert r.returncode == 0 and "8 rank(s); this process would be rank 5" in r.stdout
-    assert r.stdout.count("127.0.0.1") == 8
+    assert r.stdout.count("127.0.0.1") == 8 and "host NUMA nodes:" in r.stdout
     bad = tmp_path / "nodefile"
     bad.write_text("0 a 1.2.3.4 notaport 0\n")
     r = subprocess.run([str(BIN / "oncillamem"), str(bad), "--check"], capture_output=True, text=True, timeout=30)
