@@ -102,9 +102,16 @@ def test_garbage_on_tcp_uds_and_mq_does_not_hurt_the_daemons():
         assert all(p.poll() is None for p in cl.procs.values())
 
 
+def _msg_version():
+    import re
+    from conftest import REPO
+
+    return int(re.search(r"kMsgVersion\s*=\s*(\d+)", (REPO / "src" / "common" / "msg.hpp").read_text()).group(1))
+
+
 def _frame(mtype, payload, status=1, rank=1, seq=77):
     """A well-formed 192-byte Message (src/common/msg.hpp): header (32 B) + 160-byte union."""
-    hdr = struct.pack("<IHHHHiiIi", 0x4F434D32, 2, mtype, status, 0, os.getpid(), rank, seq, 0)
+    hdr = struct.pack("<IHHHHiiIi", 0x4F434D32, _msg_version(), mtype, status, 0, os.getpid(), rank, seq, 0)
     hdr += bytes(32 - len(hdr))
     return hdr + payload + bytes(160 - len(payload))
 
