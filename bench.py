@@ -251,6 +251,22 @@ def run_ocm(args):
         clocks.__exit__(None, None, None)
         ok = ok and ops.verify(dst.remote_tensor(), ((0x1111 + rank) & 0xFFFFFFFFFFFFFFFF), S) == 0
 
+        # --- what the platform gives that step: K plain cudaMemcpyAsync H2D copies of the same pinned buffer into the
+        # window, all ranks at once (copy engines; baseline only).  On the 8-GPU VMs of this pool the host side, not
+        # PCIe, is the limit once more than two GPUs pull at the same time (profiles/h2d_ceiling_8gpu.jsonl).
+        rt = ctypes.CDLL("libcudart.so.12")
+        hptr, wptr = host.local_ptr, dst.local_ptr
+        sp = ctypes.c_void_p(int(stream.cuda_stream) or 1)
+        for _ in range(2):
+            rt.cudaMemcpyAsync(ctypes.c_void_p(wptr), ctypes.c_void_p(hptr), ctypes.c_size_t(S), 1, sp)
+        barrier(world)
+        ev0.record()
+        for _ in range(K):
+            rt.cudaMemcpyAsync(ctypes.c_void_p(wptr), ctypes.c_void_p(hptr), ctypes.c_size_t(S), 1, sp)
+        ev1.record()
+        barrier(world)
+        h2d_ceiling = world * S * K / (allmax(ev0.elapsed_time(ev1), world) / 1e3) / 1e9
+
         # --- GB/s versus message size, next to the copy engines (BASELINE.json metric: "GB/s vs size") ----
         curve = None
         if cmax:
@@ -301,7 +317,9 @@ def run_ocm(args):
                            "n1_note": "at 1 GPU the neighbour is the rank itself: HBM-local copy, no NVLink"},
                 "clocks": clocks.summary(),
                 "e2e": {"value": round(e2e, 2), "unit": "GB/s", "h2d_bytes_per_step": S, "d2h_bytes_per_step": 8,
-                        "path": "ocm_copy(pinned LOCAL_HOST -> REMOTE_GPU pair), sync, then read the signal word"},
+                        "path": "ocm_copy(pinned LOCAL_HOST -> REMOTE_GPU pair), sync, then read the signal word",
+                        "h2d_ceiling_GBps": round(h2d_ceiling, 2),
+                        "h2d_ceiling_note": "cudaMemcpyAsync H2D of the same buffer on all ranks at once (device-timed)"},
                 "gpu_launches": int(launches) * world,
                 "kernels": "ocm_copy_v32_kernel<dual> + ocm_complete_kernel per step",
                 **roof, "impl": "ocm", **extra,

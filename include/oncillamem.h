@@ -154,6 +154,11 @@ int      ocm_reduce_get_f32(ocm_alloc_t a, const struct ocm_params *p, void *str
  * are performed before returning. */
 int ocm_copy_async(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p, void *stream);
 int ocm_copy_onesided_async(ocm_alloc_t a, const struct ocm_params *p, void *stream);
+/* n one-sided transfers on ONE paired allocation in a single kernel launch (entry i: op_flag 1 = put
+ * window[src_offset] -> far[dest_offset], 0 = get).  Small messages are launch-bound; a batch costs one launch.
+ * The reference posts one work request and blocks once per message (src/lib.c:669-723).  Stream-ordered like the
+ * *_async calls; the far side's signal receives +<number of puts> after the last byte of the batch. */
+int ocm_copy_onesided_batch(ocm_alloc_t a, const struct ocm_params *p, int n, void *stream);
 /* Wait for everything enqueued on the library's own copy stream. */
 int ocm_quiet(void);
 
@@ -222,6 +227,10 @@ struct ocm_stats {
 };
 int ocm_get_stats(struct ocm_stats *out);            /* this process + its rank's pools */
 int ocm_get_rank_stats(int rank, struct ocm_stats *out); /* via MSG_STATS to the daemon */
+/* Resident copy server (blocking copies up to OCM_SERVER_MAX bytes, default 128 KiB, are moved by a kernel that is
+ * already running: no launch, no stream synchronisation).  Returns 1 if it is enabled in this process; *ops = copies
+ * it has served, *launches = how often the kernel had to be (re)started.  OCM_SERVER=0 disables it. */
+int ocm_server_stats(uint64_t *ops, uint64_t *launches);
 
 #ifdef __cplusplus
 }

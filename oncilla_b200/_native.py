@@ -148,6 +148,7 @@ _sig("ocm_is_multicast", C.c_int, ocm_alloc_t)
 _sig("ocm_copy_async", C.c_int, ocm_alloc_t, ocm_alloc_t, P(ocm_params), C.c_void_p)
 _sig("ocm_copy_onesided_async", C.c_int, ocm_alloc_t, P(ocm_params), C.c_void_p)
 _sig("ocm_quiet", C.c_int)
+_sig("ocm_copy_onesided_batch", C.c_int, C.c_void_p, P(ocm_params), C.c_int, C.c_void_p)
 _sig("ocm_signal_read", C.c_int, ocm_alloc_t, P(C.c_uint64))
 _sig("ocm_signal_wait", C.c_int, ocm_alloc_t, C.c_uint64, C.c_int)
 _sig("ocm_reduce_get_f32", C.c_int, ocm_alloc_t, P(ocm_params), C.c_void_p)
@@ -158,6 +159,7 @@ _sig("ocm_copy_strided", C.c_int, ocm_alloc_t, ocm_alloc_t, P(ocm_strided), C.c_
 _sig("ocm_copy_onesided_strided", C.c_int, ocm_alloc_t, P(ocm_strided), C.c_void_p)
 _sig("ocm_get_stats", C.c_int, P(ocm_stats))
 _sig("ocm_get_rank_stats", C.c_int, C.c_int, P(ocm_stats))
+_sig("ocm_server_stats", C.c_int, P(C.c_uint64), P(C.c_uint64))
 # kernel ABI
 _sig("ocmk_copy", C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p)
 _sig("ocmk_copy_tuned", C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int,

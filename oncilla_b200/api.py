@@ -232,6 +232,18 @@ class Allocation:
         """One-sided read far side[dest_offset] -> window[src_offset]."""
         _onesided(self, 0, nbytes, src_offset, dest_offset, stream)
 
+    def batch(self, entries, *, stream=None) -> None:
+        """Many one-sided transfers in ONE kernel launch.  ``entries``: iterable of ``(op, nbytes, src_offset,
+        dest_offset)`` with op "put"/1 or "get"/0.  Stream-ordered (``None`` = library stream, wait with :func:`quiet`)."""
+        entries = list(entries)
+        arr = (N.ocm_params * len(entries))()
+        for p, (op, nbytes, so, do) in zip(arr, entries):
+            p.op_flag = 1 if op in (1, "put") else 0
+            p.bytes, p.src_offset, p.dest_offset = int(nbytes), int(so), int(do)
+        r = lib.ocm_copy_onesided_batch(self.handle, arr, len(entries), C.c_void_p(_stream_ptr(stream)))
+        if r:
+            raise OcmError("ocm_copy_onesided_batch", r)
+
     def reduce_get_f32(self, nbytes: int | None = None, *, src_offset: int = 0, dest_offset: int = 0, stream=None) -> None:
         """NVLS gather-reduce: window[src_offset:] = fp32 sum over every rank's replica of far[dest_offset:].
 
@@ -340,6 +352,13 @@ def copy_strided(dst: Allocation, src: Allocation, *, row_bytes: int, counts=(1,
         r = lib.ocm_copy_strided(dst.handle, src.handle, C.byref(d), sp)
     if r:
         raise OcmError("ocm_copy_strided", r)
+
+
+def server_stats() -> dict:
+    """The resident copy server of this process: enabled?, copies served, kernel (re)starts."""
+    ops, launches = C.c_uint64(0), C.c_uint64(0)
+    on = lib.ocm_server_stats(C.byref(ops), C.byref(launches))
+    return {"enabled": bool(on), "ops": ops.value, "launches": launches.value}
 
 
 def stats(rank: int | None = None) -> dict:

@@ -28,6 +28,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 
 namespace ocmk {
 
@@ -202,6 +203,66 @@ __global__ void __launch_bounds__(256) ocm_copy_v32_kernel(CopyArgs a) {
     if (threadIdx.x == 0) finish_and_signal(a.signal, a.ticket, a.done_flag, a.done_value);
 }
 
+// ---- batched copies: one launch, many segments ------------------------------------------------------------------
+struct BatchArgs {
+    CopySeg  seg[kMaxBatch];
+    uint32_t cta_first[kMaxBatch + 1];   // CTAs [cta_first[i], cta_first[i+1]) work on segment i
+    uint32_t n;
+    uint32_t signal_add;
+    uint64_t *signal;
+    unsigned *ticket;
+    uint64_t *done_flag;
+    uint64_t  done_value;
+};
+
+__global__ void __launch_bounds__(256) ocm_copy_batch_kernel(const __grid_constant__ BatchArgs a) {
+    // which segment is mine (the table lives in constant-bank kernel parameters: a short scan is cheap)
+    uint32_t i = 0;
+    while (i + 1 < a.n && blockIdx.x >= a.cta_first[i + 1]) ++i;
+    const uint32_t part = blockIdx.x - a.cta_first[i], parts = a.cta_first[i + 1] - a.cta_first[i];
+    const uint8_t *src = static_cast<const uint8_t *>(a.seg[i].src);
+    uint8_t *dst = static_cast<uint8_t *>(a.seg[i].dst);
+    const uint64_t bytes = a.seg[i].bytes;
+    const uintptr_t r = (uintptr_t)dst & 31;
+    if (((uintptr_t)src & 31) == r) {
+        uint64_t head = (32 - r) & 31;
+        if (head > bytes) head = bytes;
+        const uint64_t n = (bytes - head) / 32;
+        const uint64_t stride = (uint64_t)parts * blockDim.x;
+        uint64_t k = (uint64_t)part * blockDim.x + threadIdx.x;
+        for (; k + stride < n; k += 2 * stride) {
+            V32 v0 = ld_v32(src + head + k * 32), v1 = ld_v32(src + head + (k + stride) * 32);
+            st_v32(dst + head + k * 32, v0);
+            st_v32(dst + head + (k + stride) * 32, v1);
+        }
+        for (; k < n; k += stride) st_v32(dst + head + k * 32, ld_v32(src + head + k * 32));
+        if (part == 0) {
+            const uint64_t tail0 = head + n * 32;
+            for (uint64_t o = threadIdx.x; o < head + (bytes - tail0); o += blockDim.x) {
+                const uint64_t b = o < head ? o : tail0 + (o - head);
+                dst[b] = src[b];
+            }
+        }
+    } else {
+        for (uint64_t b = (uint64_t)part * blockDim.x + threadIdx.x; b < bytes; b += (uint64_t)parts * blockDim.x) dst[b] = src[b];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && (a.signal || a.done_flag)) {
+        bool last = true;
+        if (gridDim.x > 1) {
+            unsigned t;
+            asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(t) : "l"(a.ticket) : "memory");
+            last = (t == gridDim.x - 1);
+            if (last) atomicExch(a.ticket, 0u);
+        }
+        if (last) {
+            asm volatile("fence.acq_rel.sys;" ::: "memory");
+            if (a.signal) red_release_sys_add(a.signal, (uint64_t)a.signal_add);
+            if (a.done_flag) st_release_sys(a.done_flag, a.done_value);
+        }
+    }
+}
+
 __global__ void ocm_signal_kernel(uint64_t *signal) {
     __threadfence_system();
     red_release_sys_add(signal, 1ull);
@@ -360,6 +421,44 @@ cudaError_t launch_copy(void *dst, void *dst2, const void *src, size_t bytes, ui
     }
     if (launches) ++*launches;
     return cudaGetLastError();
+}
+
+cudaError_t launch_copy_batch(const CopySeg *segs, int n, uint64_t *signal, unsigned *ticket, cudaStream_t stream,
+                              unsigned long long *launches, const CopyNotify *notify) {
+    if (n <= 0) return cudaSuccess;
+    if ((signal || notify) && !ticket) return cudaErrorInvalidValue;
+    const int sms = num_sms();
+    for (int base = 0; base < n; base += kMaxBatch) {
+        const int m = std::min(kMaxBatch, n - base);
+        const bool final_launch = base + m >= n;
+        BatchArgs a;
+        memset(&a, 0, sizeof a);
+        a.n = (uint32_t)m;
+        // CTAs per segment: one per 16 KiB, the whole launch capped at four CTAs per SM
+        uint64_t total = 0;
+        for (int i = 0; i < m; ++i) total += segs[base + i].bytes;
+        const uint64_t cap = (uint64_t)sms * 4;
+        uint32_t next = 0;
+        for (int i = 0; i < m; ++i) {
+            a.seg[i] = segs[base + i];
+            uint64_t want = std::max<uint64_t>(1, (a.seg[i].bytes + 16383) / 16384);
+            if (total > cap * 16384) want = std::max<uint64_t>(1, a.seg[i].bytes * cap / total);
+            a.cta_first[i] = next;
+            next += (uint32_t)want;
+        }
+        a.cta_first[m] = next;
+        // the completion of a long list is published by its last launch (stream order covers the earlier ones)
+        a.signal = final_launch ? signal : nullptr;
+        a.signal_add = (uint32_t)n;
+        a.ticket = ticket;
+        a.done_flag = final_launch && notify ? notify->flag : nullptr;
+        a.done_value = notify ? notify->value : 0;
+        ocm_copy_batch_kernel<<<next, 256, 0, stream>>>(a);
+        if (launches) ++*launches;
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
 }
 
 cudaError_t launch_signal(uint64_t *signal, cudaStream_t stream) {

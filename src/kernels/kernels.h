@@ -40,6 +40,18 @@ cudaError_t launch_copy(void *dst, void *dst2, const void *src, size_t bytes, ui
                         cudaStream_t stream, const CopyTuning *tuning = nullptr, unsigned long long *launches = nullptr,
                         const CopyNotify *notify = nullptr);
 
+// Many contiguous copies in ONE launch (small-message batching): segment i moves seg[i].bytes from seg[i].src to
+// seg[i].dst.  Every CTA works on a slice of one segment.  signal (optional) receives +n after the last byte of the
+// whole batch.  n <= kMaxBatch per launch; launch_copy_batch loops for longer lists.
+constexpr int kMaxBatch = 64;
+struct CopySeg {
+    const void *src;
+    void       *dst;
+    uint64_t    bytes;
+};
+cudaError_t launch_copy_batch(const CopySeg *segs, int n, uint64_t *signal, unsigned *ticket, cudaStream_t stream,
+                              unsigned long long *launches = nullptr, const CopyNotify *notify = nullptr);
+
 // ---- K9: fill / verify / checksum --------------------------------------------
 cudaError_t launch_fill(void *dst, size_t bytes, uint64_t pattern, cudaStream_t stream);
 // *mismatches (device or mapped host, u64) += number of 8-byte words != pattern (+ tail bytes)
@@ -96,6 +108,31 @@ cudaError_t launch_gups_init(const GupsTable &t, int my_rank, cudaStream_t strea
 size_t sort_scratch_bytes(uint64_t n, int *ctas_out = nullptr);
 cudaError_t launch_sort_u64(uint64_t *keys, uint64_t *tmp, uint64_t n, void *scratch, size_t scratch_bytes,
                             cudaStream_t stream, unsigned long long *launches = nullptr);
+
+// ---- H2: resident copy server ----------------------------------------------------------
+// Descriptor ring + control block live in pinned, mapped host memory (the host posts, the kernel polls).
+struct alignas(64) ServerDesc {
+    const void *src;
+    void       *dst;
+    void       *dst2;       // optional second destination
+    uint64_t    bytes;
+    uint64_t   *signal;     // optional completion counter of the destination allocation (+1, release.sys)
+    uint64_t    pad[2];
+    uint64_t    seq;        // written last (release): descriptor i is valid once seq == i + 1
+};
+enum ServerState : uint32_t { SERVER_EXITED = 0, SERVER_RUNNING = 1, SERVER_EXITING = 2 };
+struct ServerCtl {
+    alignas(64) uint32_t state;   // ServerState; host: EXITED -> RUNNING (before a launch), kernel: the rest
+    alignas(64) uint64_t done;    // descriptors completed so far (kernel, release.sys; in order)
+    // phase accounting, added up by the kernel when it leaves (one writer; read with OCM_SERVER_TRACE=1 at ocm_tini):
+    // descriptors served, ns spent copying / in the completion fence + stores, empty polls of the ring and ns in them
+    alignas(64) uint64_t t_ops;
+    uint64_t t_copy_ns, t_fence_ns, t_polls, t_poll_ns;
+};
+// Starts the one-CTA server on `stream`: it serves descriptors from `start_seq` on and leaves after `idle_ns`
+// without work or `max_ns` of life (see server.cu for the exit hand-shake).
+cudaError_t launch_copy_server(ServerDesc *ring, uint32_t ring_size, ServerCtl *ctl, uint64_t start_seq, uint64_t idle_ns,
+                               uint64_t max_ns, cudaStream_t stream);
 
 int num_sms(int device = -1);
 // Launches made by entry points that live inside the kernel library (ocmk_sort_u64_noalloc, the copy server);

@@ -518,6 +518,7 @@ int ocm_init(void) {
             }
         }
     }
+    server_init();
     std::string e2;
     if (shm_open_existing(shm_cluster_name(), &c.cluster_map, &e2)) {
         auto *ct = static_cast<ClusterTable *>(c.cluster_map.base);
@@ -549,6 +550,7 @@ int ocm_tini(void) {
     }
     if (!left.empty()) LOGW("%zu allocation(s) still live at ocm_tini: releasing", left.size());
     for (auto *a : left) ocm_free(a);
+    server_shutdown();
     if (c.device >= 0) {
         DeviceGuard dg(c.device);
         if (c.stream) {

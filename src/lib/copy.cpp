@@ -18,6 +18,7 @@
 #include "trace.hpp"
 #include "../common/log.hpp"
 #include "../kernels/kernels.h"
+#include <algorithm>
 #include <cstring>
 #include <cuda_runtime.h>
 
@@ -38,12 +39,28 @@ struct SyncNotify {
     uint64_t value = 0;
     int gpu_ops = 0;        // kernels / async memcpys enqueued by the current call
     int notified = 0;       // ... of which carry the completion word
+    int server_ops = 0;     // copies handed to the resident copy server (H2) by the current call
+    bool server_waited = false;
+    uint64_t server_seq = 0;
+    std::atomic<uint64_t> *server_sig = nullptr;   // completion counter the HOST bumps once the server reports done
+    uint64_t async_snap = 0;    // Ctx::lib_async_issued when the call began
     ocmk::CopyNotify cn{nullptr, 0};
 };
 static thread_local SyncNotify t_sn;
 
 // Only kernels that already publish a completion signal carry the word: for those the system fence is paid
 // anyway (measured: a get without signal gets 2 us SLOWER with the extra fence + host store, a put 1 us faster).
+// Wait for the copy this call handed to the resident server, then publish its completion signal.  The kernel's
+// done word is released at system scope after its bytes, so counting on the CPU side (the allocation's CPU word:
+// one writing agent per word) keeps the order "bytes, then signal" and saves the kernel a second PCIe round trip.
+static int server_drain() {
+    if (!t_sn.server_ops || t_sn.server_waited) return OCM_OK;
+    t_sn.server_waited = true;
+    const int e = server_wait(t_sn.server_seq);
+    if (!e && t_sn.server_sig) t_sn.server_sig->fetch_add(1, std::memory_order_release);
+    return e;
+}
+
 static const ocmk::CopyNotify *note_kernel(bool has_signal) {
     ++t_sn.gpu_ops;
     if (!t_sn.armed || !has_signal) return nullptr;
@@ -210,6 +227,8 @@ int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2
               uint64_t bytes, const Side *sig, void *stream, bool *used_stream) {
     Ctx &c = ctx();
     LaunchFlush flush_launches;
+    // only the first hop of a blocking call may go through the copy server; anything after it waits for it first
+    if (int e = server_drain()) return e;
     if (!dst.ptr || !src.ptr || (dst2 && !dst2->ptr)) return OCM_EINVAL;
     if (!fits(src, src_off, bytes) || !fits(dst, dst_off, bytes) || (dst2 && !fits(*dst2, dst2_off, bytes)))
         return OCM_ERANGE;
@@ -259,6 +278,16 @@ int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2
     const bool fused = kernel_addressable(src) && kernel_addressable(dst) && (!dst2 || kernel_addressable(*dst2)) &&
                        ((src.tier == TIER_GPU && dst.tier == TIER_GPU && (!dst2 || dst2->tier == TIER_GPU)) ||
                         (dst2 && gpu_dst));
+    uint64_t srv_seq = 0;
+    if (fused && t_sn.armed && !stream && !*used_stream && t_sn.gpu_ops == 0 && t_sn.server_ops == 0 && server_eligible(bytes) &&
+        server_post((const char *)src.ptr + src_off, (char *)dst.ptr + dst_off, dst2 ? (char *)dst2->ptr + dst2_off : nullptr,
+                    bytes, signal_cpu ? nullptr : signal, &srv_seq)) {
+        // H2: a blocking small copy - the resident kernel moves it, nothing is launched (finish_sync waits for it)
+        t_sn.server_ops = 1;
+        t_sn.server_seq = srv_seq;
+        t_sn.server_sig = signal ? signal_cpu : nullptr;
+        return OCM_OK;
+    }
     if (fused) {
         *used_stream = true;
         err = cuda_err(ocmk::launch_copy((char *)dst.ptr + dst_off, dst2 ? (char *)dst2->ptr + dst2_off : nullptr,
@@ -477,6 +506,7 @@ static thread_local DoneSlot t_done_slot;
 static void arm_sync_notify() {
     Ctx &c = ctx();
     t_sn = SyncNotify();
+    t_sn.async_snap = c.lib_async_issued.load(std::memory_order_acquire);
     if (!c.done_word || c.device < 0) return;
     const int s = t_done_slot.get();
     if (s < 0) return;
@@ -488,6 +518,8 @@ static void arm_sync_notify() {
 
 static int finish_sync(int err, bool used, void *stream) {
     Ctx &c = ctx();
+    if (const int e = server_drain())
+        if (!err) err = e;
     if (used && c.device >= 0) {
         bool done = false;
         if (!err && !stream && t_sn.armed && t_sn.gpu_ops == 1 && t_sn.notified == 1) {
@@ -513,6 +545,7 @@ static int finish_sync(int err, bool used, void *stream) {
             cudaError_t e = cudaStreamSynchronize((cudaStream_t)(stream ? stream : c.stream));
             if (e != cudaSuccess && !err) err = cuda_err(e, "stream sync");
         }
+        if (!stream) c.note_lib_synced(t_sn.async_snap);   // the library stream has drained up to this call
     }
     t_sn = SyncNotify();
     set_last_error(err);
@@ -544,6 +577,7 @@ extern "C" {
 int ocm_copy_async(ocm_alloc_t dst, ocm_alloc_t src, const struct ocm_params *p, void *stream) {
     TraceRange tr_("ocm_copy_async");
     bool used = false;
+    if (!stream) ctx().note_lib_async();
     int err = do_copy(dst, src, p, stream, &used);
     set_last_error(err);
     return -err;
@@ -560,6 +594,7 @@ int ocm_copy(ocm_alloc_t dst, ocm_alloc_t src, ocm_param_t p) {
 int ocm_copy_onesided_async(ocm_alloc_t a, const struct ocm_params *p, void *stream) {
     TraceRange tr_("ocm_copy_onesided_async");
     bool used = false;
+    if (!stream) ctx().note_lib_async();
     int err = do_onesided(a, p, stream, &used);
     set_last_error(err);
     return -err;
@@ -571,6 +606,73 @@ int ocm_copy_onesided(ocm_alloc_t a, ocm_param_t p) {
     arm_sync_notify();
     int err = do_onesided(a, p, nullptr, &used);
     return finish_sync(err, used, nullptr);
+}
+
+// Many one-sided transfers on one pair in a single kernel launch (entry i: op_flag 1 = window[src_offset] ->
+// far[dest_offset], 0 = the reverse).  Small messages are launch-bound (~2 us of device time each, more on the host);
+// batching them is what a resident work queue would do, without the resident kernel.  Stream-ordered like the
+// *_async calls; the far side's signal word receives +<number of puts> once every byte of the batch is visible.
+int ocm_copy_onesided_batch(ocm_alloc_t a, const struct ocm_params *p, int n, void *stream) {
+    TraceRange tr_("ocm_copy_onesided_batch");
+    Ctx &c = ctx();
+    if (!valid(a) || (!p && n > 0) || n < 0) {
+        set_last_error(OCM_EINVAL);
+        return -OCM_EINVAL;
+    }
+    if (n == 0) return 0;
+    const Side *far = far_side(a);
+    bool used = false;
+    int err = OCM_OK;
+    const bool one_kernel = a->stripes.empty() && far && a->local.valid() && c.device >= 0 && kernel_addressable(*far) &&
+                            kernel_addressable(a->local) && (far->tier == TIER_GPU || a->local.tier == TIER_GPU);
+    if (stale(a)) err = OCM_ESTALE;
+    else if (!one_kernel) {
+        if (!stream) c.note_lib_async();
+        for (int i = 0; i < n && !err; ++i) err = do_onesided(a, &p[i], stream, &used);
+    } else {
+        std::vector<ocmk::CopySeg> segs((size_t)n);
+        int puts = 0;
+        for (int i = 0; i < n && !err; ++i) {
+            if (p[i].bytes > a->local.bytes || !fits(a->local, p[i].src_offset, p[i].bytes) ||
+                !fits(*far, p[i].dest_offset, p[i].bytes)) {
+                err = OCM_ERANGE;
+                break;
+            }
+            char *w = (char *)a->local.ptr + p[i].src_offset, *f = (char *)far->ptr + p[i].dest_offset;
+            segs[i].src = p[i].op_flag ? w : f;
+            segs[i].dst = p[i].op_flag ? f : w;
+            segs[i].bytes = p[i].bytes;
+            puts += p[i].op_flag != 0;
+        }
+        if (!err) {
+            DeviceGuard dg(c.device);
+            if (!stream) c.note_lib_async();
+            unsigned long long nl = 0;
+            // the signal counts puts only; a batch of gets publishes nothing
+            uint64_t *sig = puts ? far->gpu_signal() : nullptr;
+            cudaError_t e = cudaSuccess;
+            if (puts == n || puts == 0) {
+                e = ocmk::launch_copy_batch(segs.data(), n, sig, next_ticket(), (cudaStream_t)(stream ? stream : c.stream), &nl);
+            } else {
+                // mixed directions: puts first (they carry the signal), then the gets
+                std::stable_partition(segs.begin(), segs.end(), [&](const ocmk::CopySeg &s) {
+                    return (const char *)s.dst >= (const char *)far->ptr && (const char *)s.dst < (const char *)far->ptr + far->bytes;
+                });
+                e = ocmk::launch_copy_batch(segs.data(), puts, sig, next_ticket(), (cudaStream_t)(stream ? stream : c.stream), &nl);
+                if (e == cudaSuccess)
+                    e = ocmk::launch_copy_batch(segs.data() + puts, n - puts, nullptr, next_ticket(),
+                                                (cudaStream_t)(stream ? stream : c.stream), &nl);
+            }
+            c.kernel_launches.fetch_add(nl, std::memory_order_relaxed);
+            c.n_copies.fetch_add((uint64_t)n, std::memory_order_relaxed);
+            for (int i = 0; i < n; ++i) c.copy_bytes.fetch_add(p[i].bytes, std::memory_order_relaxed);
+            err = cuda_err(e, "batched copy kernel");
+            used = true;
+        }
+    }
+    mark_pending(a, stream, used);
+    set_last_error(err);
+    return -err;
 }
 
 // NVLS gather-reduce (K6, multimem.ld_reduce): window = sum over all ranks' replicas.  Stream-ordered like the
@@ -588,6 +690,7 @@ int ocm_reduce_get_f32(ocm_alloc_t a, const struct ocm_params *p, void *stream) 
     else if ((p->src_offset | p->dest_offset | p->bytes) & 15) err = OCM_EINVAL;
     if (!err && p->bytes) {
         DeviceGuard dg(c.device);
+        if (!stream) c.note_lib_async();
         err = cuda_err(ocmk::launch_get_reduce_f32((char *)a->local.ptr + p->src_offset, (const char *)a->mc_ptr + p->dest_offset,
                                                    p->bytes, (cudaStream_t)(stream ? stream : c.stream)),
                        "multimem reduce");
@@ -605,7 +708,10 @@ int ocm_quiet(void) {
     Ctx &c = ctx();
     if (c.device < 0 || !c.stream) return 0;
     DeviceGuard dg(c.device);
-    return cudaStreamSynchronize((cudaStream_t)c.stream) == cudaSuccess ? 0 : -OCM_ECUDA;
+    const uint64_t snap = c.lib_async_issued.load(std::memory_order_acquire);
+    if (cudaStreamSynchronize((cudaStream_t)c.stream) != cudaSuccess) return -OCM_ECUDA;
+    c.note_lib_synced(snap);
+    return 0;
 }
 
 int ocm_copy_in(ocm_alloc_t dst, void *src) {

@@ -5,6 +5,7 @@
 #include "../common/msg.hpp"
 #include "../common/tables.hpp"
 #include "../ipc/pmsg.hpp"
+#include "../kernels/kernels.h"
 #include "../../include/oncillamem.h"
 #include <atomic>
 #include <mutex>
@@ -26,6 +27,19 @@ struct RankView {
     bool         gpu_tried = false;
     gpu::PoolMapping gpu;       // ptr == nullptr if the rank has no HBM pool or we have no GPU
     uint64_t     access_mask = 0;   // devices of this process that may touch `gpu` (bit = CUDA ordinal)
+};
+
+// Host half of the resident copy server (H2; kernels/server.cu, lib/server.cpp).
+constexpr uint32_t kServerRing = 64;
+struct CopyServer {
+    bool        enabled = false;
+    void       *stream = nullptr;           // the stream the resident kernel lives on
+    ocmk::ServerDesc *ring = nullptr;       // pinned + mapped
+    ocmk::ServerCtl  *ctl = nullptr;
+    std::mutex  mu;                         // posting threads, one at a time
+    uint64_t    next_seq = 0;
+    uint64_t    max_bytes = 0, idle_ns = 0, max_ns = 0;
+    std::atomic<uint64_t> n_ops{0}, n_launches{0};
 };
 
 // A second GPU this process launches kernels on: the OWNER of a far side, so that a large put runs as
@@ -125,6 +139,20 @@ struct Ctx {
     uint64_t    *done_word = nullptr;          // kDoneSlots slots of 8 words each
     std::atomic<uint64_t> done_slots_free{0};  // bit s set: slot s is free
     uint64_t     done_seq[64] = {0};           // last sequence number handed out per slot (owner thread only)
+    CopyServer   server;
+    // *_async calls on the library stream count up `issued`; waiting for that stream moves `synced` up to the count
+    // seen before the wait began.  While synced < issued a blocking copy must queue behind that work on the stream
+    // instead of overtaking it through the copy server.
+    std::atomic<uint64_t> lib_async_issued{0}, lib_async_synced{0};
+    void note_lib_async() { lib_async_issued.fetch_add(1, std::memory_order_acq_rel); }
+    // everything counted up to `snap` (taken BEFORE the work that was waited for was enqueued) has completed
+    void note_lib_synced(uint64_t snap) {
+        uint64_t cur = lib_async_synced.load(std::memory_order_relaxed);
+        while (cur < snap && !lib_async_synced.compare_exchange_weak(cur, snap, std::memory_order_acq_rel)) {}
+    }
+    bool lib_async_pending() const {
+        return lib_async_synced.load(std::memory_order_acquire) < lib_async_issued.load(std::memory_order_acquire);
+    }
     gpu::McObject mc;            // rank 0's multicast object mapped for our device
     bool         mc_tried = false;
     // Puts at least this large are pulled by the owner GPU (0: never, the default).  Measured on 2xB200:
@@ -145,6 +173,13 @@ RankView *get_view(int rank, bool with_gpu);
 // Exchange one message with the local daemon.  0 or positive ocm_err.
 int daemon_call(Message &m, int timeout_ms = 10000);
 unsigned *next_ticket();
+
+// resident copy server (server.cpp)
+void server_init();
+void server_shutdown();
+bool server_eligible(uint64_t bytes);
+bool server_post(const void *src, void *dst, void *dst2, uint64_t bytes, uint64_t *signal, uint64_t *seq_out);
+int  server_wait(uint64_t seq);
 
 // copy engine (copy.cpp)
 int side_copy(const Side &dst, uint64_t dst_off, const Side *dst2, uint64_t dst2_off, const Side &src, uint64_t src_off,

@@ -216,6 +216,7 @@ static int strided_sides(const Side &dst, const Side &src, const struct ocm_stri
     }
     DeviceGuard dg(c.device);
     cudaStream_t st = (cudaStream_t)(stream ? stream : c.stream);
+    if (!stream) c.note_lib_async();
     c.n_copies.fetch_add(1, std::memory_order_relaxed);
     c.copy_bytes.fetch_add(d->extent[0] * n[0] * n[1] * n[2], std::memory_order_relaxed);
     unsigned long long nl = 0;

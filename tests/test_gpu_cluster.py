@@ -391,6 +391,96 @@ def test_native_ocm_test_program_gpu(gpu_cluster):
         assert "pass: OCM test completed successfully" in r.stdout
 
 
+def test_batched_onesided_copies_one_launch(gpu_cluster):
+    """ocm_copy_onesided_batch: 100 scattered small puts (odd sizes and alignments among them) cost 2 launches
+    (64 segments per launch), land byte-exact, and the signal counts every put; gets come back the same way."""
+    n_msg, span = 100, 1 << 20
+    a = ocm.alloc(ocm.OCM_REMOTE_GPU, span, span)
+    g = torch.Generator().manual_seed(11)
+    ref = torch.randint(0, 256, (span,), dtype=torch.uint8, generator=g)
+    a.local_tensor().copy_(ref.cuda())
+    torch.cuda.synchronize()
+    entries, expect = [], torch.zeros(span, dtype=torch.uint8)
+    slot = span // n_msg
+    for i in range(n_msg):
+        nbytes = int(torch.randint(1, slot - 64, (1,), generator=g))
+        so = i * slot + int(torch.randint(0, 32, (1,), generator=g))
+        do = i * slot + (so % 32 if i % 3 else int(torch.randint(0, 32, (1,), generator=g)))   # some congruent mod 32, some not
+        entries.append(("put", nbytes, so, do))
+        expect[do:do + nbytes] = ref[so:so + nbytes]
+    lc = ops.launch_count()
+    a.batch(entries)
+    ocm.quiet()
+    assert ops.launch_count() - lc == 2
+    assert a.signal() == n_msg
+    assert torch.equal(a.remote_tensor().cpu(), expect)
+    # and back: window <- far side, swapped offsets
+    a.local_tensor().zero_()
+    torch.cuda.synchronize()
+    a.batch([("get", nb, do, so) for (_, nb, so, do) in entries])        # window[do..] <- far[so..]
+    ocm.quiet()
+    back = a.local_tensor().cpu()
+    for (_, nb, so, do) in entries:
+        assert torch.equal(back[do:do + nb], expect[so:so + nb])
+    assert a.signal() == n_msg                                           # gets do not signal
+    with pytest.raises(ocm.OcmError):
+        a.batch([("put", 16, span - 8, 0)])                              # out of range: refused as a whole
+    a.free()
+
+
+def test_resident_copy_server_serves_small_blocking_copies(gpu_cluster):
+    """H2: blocking copies up to OCM_SERVER_MAX bytes are moved by the resident kernel (no launch); the kernel leaves
+    when idle and comes back on demand; work queued asynchronously on the library stream is never overtaken."""
+    import time
+
+    s0 = ocm.server_stats()
+    assert s0["enabled"]
+    n = 48 << 10
+    a = ocm.alloc(ocm.OCM_REMOTE_GPU, 4 << 20, 4 << 20)
+    w = a.local_tensor()
+    launches0 = ops.launch_count()
+    for i in range(20):
+        ops.fill(w[i * n:(i + 1) * n], 0xABCD000000000000 | i)
+    torch.cuda.synchronize()
+    lc = ops.launch_count()
+    for i in range(20):                                                  # back to back: the kernel stays resident
+        a.put(n, src_offset=i * n, dest_offset=(19 - i) * n)             # blocking: through the server
+        assert a.signal() == i + 1
+    assert ops.launch_count() - lc <= 2, "kernels were launched for small blocking puts"
+    for i in range(20):
+        assert ops.verify(a.remote_tensor()[(19 - i) * n:(20 - i) * n], 0xABCD000000000000 | i, n) == 0
+    s1 = ocm.server_stats()
+    assert s1["ops"] - s0["ops"] == 20 and 1 <= s1["launches"] - s0["launches"] <= 2
+    # unaligned pieces and odd sizes take the bytewise path of the server
+    h = ocm.alloc(ocm.OCM_LOCAL_HOST, 1 << 16)
+    ref = torch.arange(1 << 16, dtype=torch.int32).to(torch.uint8)
+    h.local_tensor().copy_(ref)
+    ocm.copy(a, h, 1001, src_offset=3, dest_offset=7, src_offset_2=7, dest_offset_2=13)
+    assert torch.equal(a.local_tensor()[7:7 + 1001].cpu(), ref[3:3 + 1001])
+    assert torch.equal(a.remote_tensor()[13:13 + 1001].cpu(), ref[3:3 + 1001])
+    # the kernel is resident on demand only: after an idle spell it has left (synchronize returns) and is restarted
+    time.sleep(0.05)
+    t0 = time.perf_counter()
+    torch.cuda.synchronize()
+    assert time.perf_counter() - t0 < 0.05
+    a.get(n)
+    s2 = ocm.server_stats()
+    assert s2["launches"] > s1["launches"] and s2["ops"] > s1["ops"]
+    # stream order: a big asynchronous put on the library stream, then a small blocking get of its last bytes
+    big = 4 << 20
+    ops.fill(w, 0x1122334455667788)
+    torch.cuda.synchronize()
+    a.put(big, stream=None)                                                # async, library stream
+    ops.fill(w[:4096], 0)
+    torch.cuda.synchronize()
+    a.get(4096, src_offset=0, dest_offset=big - 4096)                      # must queue behind the put
+    assert ops.verify(w[:4096], 0x1122334455667788, 4096) == 0
+    ocm.quiet()
+    assert ops.launch_count() > launches0
+    a.free()
+    h.free()
+
+
 def test_blocking_copies_from_many_threads_gpu(gpu_cluster):
     """eight threads of one process issue blocking GPU copies at once; each waits on its OWN
     completion slot, so no call may return before its own kernel has run (tests/cpp/ocm_mt.c checks every byte
