@@ -172,6 +172,11 @@ void shm_close(ShmMapping *m, bool unlink_it) {
 
 // ---------------------------------------------------------------- layout --
 static inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+// slabs per tier: never more than the pool has granules, a whole number of classes
+static inline uint32_t slab_count(uint64_t n_granules) {
+    return (uint32_t)(std::min<uint64_t>(kMaxSlabs, n_granules) / kSlabClasses * kSlabClasses);
+}
+constexpr int32_t kSlabOwnerPid = -2;   // owner_pid of the granule block that backs a slab
 
 size_t table_segment_bytes(uint64_t gpu_pool_bytes, uint64_t host_pool_bytes, uint64_t gg, uint64_t hg) {
     if (!gg) gg = default_granule(gpu_pool_bytes, TIER_GPU);
@@ -181,6 +186,8 @@ size_t table_segment_bytes(uint64_t gpu_pool_bytes, uint64_t host_pool_bytes, ui
     for (size_t n : {n_gpu, n_host}) {
         total += round_up(n * sizeof(Region), 4096);
         total += round_up((n + 63) / 64 * 8, 4096);
+        total += round_up((size_t)slab_count(n) * sizeof(Slab), 4096);
+        total += round_up((size_t)slab_count(n) * kSlabSubs * sizeof(Region), 4096);
     }
     total += round_up((size_t)kSigExtRecords * sizeof(SigExt), 4096);
     return total;
@@ -220,7 +227,13 @@ void table_format(void *base, size_t seg_bytes, int rank, int n_ranks, int daemo
             auto *bm = table_bitmap(h, t);
             bm[p.bitmap_words - 1].store(~((1ull << (p.n_granules & 63)) - 1), std::memory_order_relaxed);
         }
+        p.n_slabs = slab_count(p.n_granules);
+        p.slabs_offset = off;
+        off += round_up((size_t)p.n_slabs * sizeof(Slab), 4096);
+        p.subs_offset = off;
+        off += round_up((size_t)p.n_slabs * kSlabSubs * sizeof(Region), 4096);
     }
+    h->slabs_enabled.store(1);
     h->sigext_offset = off;
     h->n_sigext = kSigExtRecords;
     off += round_up((size_t)kSigExtRecords * sizeof(SigExt), 4096);
@@ -237,6 +250,8 @@ bool table_validate(const TableHeader *h, size_t mapped) {
         if (p.regions_offset + (uint64_t)p.n_granules * sizeof(Region) > mapped) return false;
         if (p.bitmap_offset + (uint64_t)p.bitmap_words * 8 > mapped) return false;
         if (p.granule & (p.granule - 1)) return false;
+        if (p.n_slabs > kMaxSlabs || p.slabs_offset + (uint64_t)p.n_slabs * sizeof(Slab) > mapped) return false;
+        if (p.subs_offset + (uint64_t)p.n_slabs * kSlabSubs * sizeof(Region) > mapped) return false;
     }
     if (h->sigext_offset + (uint64_t)h->n_sigext * sizeof(SigExt) > mapped) return false;
     return true;
@@ -245,7 +260,9 @@ bool table_validate(const TableHeader *h, size_t mapped) {
 // ------------------------------------------------------------- allocator --
 // ---------------------------------------------------- signal extensions --
 SigExt *sigext_claim(TableHeader *h, int tier, uint32_t region) {
-    Region &r = table_regions(h, tier)[region];
+    Region *rp = table_region_rec(h, tier, region);
+    if (!rp) return nullptr;
+    Region &r = *rp;
     SigExt *ext = table_sigext(h);
     uint32_t have = r.ext.load(std::memory_order_acquire);
     if (have) return &ext[have - 1];
@@ -281,12 +298,196 @@ uint64_t region_signal_total(TableHeader *h, const Region &r) {
     return v;
 }
 
+static void sub_release_clean(TableHeader *h, int tier, uint32_t slab, uint32_t sub);
+static size_t slab_trim(TableHeader *h, int tier);
+
+// A free sub-block of the class that fits `bytes`, from an active slab or from a slab made of a fresh granule.
+// OCM_ENOMEM when the class has no slab header or the pool no granule left (the caller then takes a whole granule).
+static int granule_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int rank, BlockRef *out, bool count);
+
+static int slab_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int rank, BlockRef *out) {
+    PoolDesc &p = h->pool[tier];
+    // smallest sub-block that holds the request: class c has sub-blocks of granule >> (c + 1), at least 256 bytes
+    int cls = -1;
+    for (int c = (int)kSlabClasses - 1; c >= 0; --c) {
+        const uint64_t sz = p.granule >> (c + 1);
+        if (sz >= 256 && sz >= bytes) {
+            cls = c;
+            break;
+        }
+    }
+    if (cls < 0 || p.n_slabs < kSlabClasses) return OCM_ENOMEM;
+    const uint32_t n_sub = class_subs((uint32_t)cls);
+    const uint64_t sub_size = p.granule >> (cls + 1);
+    const uint32_t per_class = p.n_slabs / kSlabClasses;
+    Slab *slabs = table_slabs(h, tier);
+    uint32_t slab = 0, bit = 0;
+    bool got = false;
+    for (int attempt = 0; attempt < 3 && !got; ++attempt) {
+        if (p.class_free[cls].load(std::memory_order_acquire) > 0) {
+            const uint32_t start = p.class_hint[cls].load(std::memory_order_relaxed) % per_class;
+            for (uint32_t k = 0; k < per_class && !got; ++k) {
+                const uint32_t i = ((start + k) % per_class) * kSlabClasses + (uint32_t)cls;
+                Slab &s = slabs[i];
+                if (s.state.load(std::memory_order_acquire) != SLAB_ACTIVE) continue;
+                uint64_t m = s.free_mask.load(std::memory_order_acquire);
+                while (m) {
+                    const uint32_t b = (uint32_t)__builtin_ctzll(m);
+                    if (s.free_mask.compare_exchange_weak(m, m & ~(1ull << b), std::memory_order_acq_rel)) {
+                        slab = i;
+                        bit = b;
+                        got = true;
+                        p.class_free[cls].fetch_sub(1, std::memory_order_acq_rel);
+                        p.class_hint[cls].store((start + k) % per_class, std::memory_order_relaxed);
+                        break;
+                    }
+                }
+            }
+            if (got) break;
+        }
+        // no free sub-block anywhere: turn a fresh granule into a slab of this class
+        uint32_t fresh = UINT32_MAX;
+        for (uint32_t k = 0; k < per_class; ++k) {
+            const uint32_t i = k * kSlabClasses + (uint32_t)cls;
+            uint32_t expect = SLAB_FREE;
+            if (slabs[i].state.load(std::memory_order_relaxed) == SLAB_FREE &&
+                slabs[i].state.compare_exchange_strong(expect, SLAB_INIT, std::memory_order_acq_rel)) {
+                fresh = i;
+                break;
+            }
+        }
+        if (fresh == UINT32_MAX) {
+            if (p.class_free[cls].load(std::memory_order_acquire) > 0) continue;   // somebody freed one meanwhile
+            return OCM_ENOMEM;
+        }
+        BlockRef g;
+        int err = granule_alloc(h, tier, p.granule, kSlabOwnerPid, rank, &g, false);
+        if (err) {
+            slabs[fresh].state.store(SLAB_FREE, std::memory_order_release);
+            return err;
+        }
+        Slab &s = slabs[fresh];
+        s.region = g.region;
+        s.backing_id = g.id;
+        // sub-block 0 is ours, the others are published with the mask (release: region/backing_id first)
+        const uint64_t all = n_sub == 64 ? ~0ull : ((1ull << n_sub) - 1);
+        s.free_mask.store(all & ~1ull, std::memory_order_release);
+        s.state.store(SLAB_ACTIVE, std::memory_order_release);
+        p.class_free[cls].fetch_add((int64_t)n_sub - 1, std::memory_order_acq_rel);
+        slab = fresh;
+        bit = 0;
+        got = true;
+    }
+    if (!got) return OCM_ENOMEM;
+    Slab &s = slabs[slab];
+    Region &r = table_subs(h, tier)[(size_t)slab * kSlabSubs + bit];
+    r.n_granules = 0;
+    r.owner_pid = pid;
+    r.owner_rank = rank;
+    r.bytes = bytes;
+    r.id = h->next_id.fetch_add(1, std::memory_order_relaxed);
+    r.generation += 1;
+    r.attached.store(0, std::memory_order_relaxed);
+    r.ext.store(0, std::memory_order_relaxed);
+    r.signal.store(0, std::memory_order_relaxed);
+    r.signal_cpu.store(0, std::memory_order_relaxed);
+    r.state.store(REGION_LIVE, std::memory_order_release);
+    p.sub_live.fetch_add(1, std::memory_order_relaxed);
+    p.sub_bytes.fetch_add(sub_size, std::memory_order_relaxed);
+    p.live.fetch_add(1, std::memory_order_relaxed);
+    p.total_allocs.fetch_add(1, std::memory_order_relaxed);
+    out->region = kSlabFlag | (slab << 6) | bit;
+    out->generation = r.generation;
+    out->offset = (uint64_t)s.region * p.granule + (uint64_t)bit * sub_size;
+    out->block_bytes = sub_size;
+    out->id = r.id;
+    return OCM_OK;
+}
+
+// The sub-block is clean again: publish it; a slab that is completely free goes back to the pool when the class
+// keeps at least another slab's worth of free sub-blocks (no create/retire ping-pong around one small block).
+static void sub_release_clean(TableHeader *h, int tier, uint32_t slab, uint32_t sub) {
+    PoolDesc &p = h->pool[tier];
+    Slab &s = table_slabs(h, tier)[slab];
+    const uint32_t cls = slab_class(slab), n_sub = class_subs(cls);
+    const uint64_t all = n_sub == 64 ? ~0ull : ((1ull << n_sub) - 1);
+    const uint64_t before = s.free_mask.fetch_or(1ull << sub, std::memory_order_acq_rel);
+    const int64_t free_now = p.class_free[cls].fetch_add(1, std::memory_order_acq_rel) + 1;
+    if ((before | (1ull << sub)) != all || free_now < 2 * (int64_t)n_sub) return;
+    uint64_t expect = all;
+    if (!s.free_mask.compare_exchange_strong(expect, 0, std::memory_order_acq_rel)) return;   // somebody took a block
+    s.state.store(SLAB_RETIRING, std::memory_order_release);
+    p.class_free[cls].fetch_sub((int64_t)n_sub, std::memory_order_acq_rel);
+    const uint32_t region = s.region;
+    const uint64_t id = s.backing_id;
+    pool_free(h, tier, region, id);
+    s.state.store(SLAB_FREE, std::memory_order_release);
+}
+
+// Retire every slab that has no live sub-block.  Returns how many granules went back.
+static size_t slab_trim(TableHeader *h, int tier) {
+    PoolDesc &p = h->pool[tier];
+    Slab *slabs = table_slabs(h, tier);
+    size_t n = 0;
+    for (uint32_t i = 0; i < p.n_slabs; ++i) {
+        Slab &s = slabs[i];
+        if (s.state.load(std::memory_order_acquire) != SLAB_ACTIVE) continue;
+        const uint32_t cls = slab_class(i), n_sub = class_subs(cls);
+        uint64_t expect = n_sub == 64 ? ~0ull : ((1ull << n_sub) - 1);
+        if (!s.free_mask.compare_exchange_strong(expect, 0, std::memory_order_acq_rel)) continue;
+        s.state.store(SLAB_RETIRING, std::memory_order_release);
+        p.class_free[cls].fetch_sub((int64_t)n_sub, std::memory_order_acq_rel);
+        const uint32_t region = s.region;
+        const uint64_t id = s.backing_id;
+        pool_free(h, tier, region, id);
+        s.state.store(SLAB_FREE, std::memory_order_release);
+        ++n;
+    }
+    return n;
+}
+
+static int sub_free(TableHeader *h, int tier, uint32_t region, uint64_t id) {
+    PoolDesc &p = h->pool[tier];
+    Region *rp = table_region_rec(h, tier, region);
+    if (!rp) return OCM_EINVAL;
+    Region &r = *rp;
+    if (r.state.load(std::memory_order_acquire) != REGION_LIVE || r.id != id) return OCM_ESTALE;
+    const bool scrub = h->scrub_enabled.load(std::memory_order_relaxed) != 0;
+    uint32_t expect = REGION_LIVE;
+    if (!r.state.compare_exchange_strong(expect, scrub ? REGION_DIRTY : REGION_FREE, std::memory_order_acq_rel))
+        return OCM_ESTALE;
+    sigext_release(h, r);
+    const uint32_t slab = sub_slab(region), sub = sub_index(region);
+    const uint64_t sub_size = p.granule >> (slab_class(slab) + 1);
+    p.sub_live.fetch_sub(1, std::memory_order_relaxed);
+    p.sub_bytes.fetch_sub(sub_size, std::memory_order_relaxed);
+    p.live.fetch_sub(1, std::memory_order_relaxed);
+    p.total_frees.fetch_add(1, std::memory_order_relaxed);
+    if (scrub) {
+        p.dirty_bytes.fetch_add(sub_size, std::memory_order_relaxed);
+        stack_push(p.sub_dirty_head, table_subs(h, tier), slab * kSlabSubs + sub);
+    } else {
+        sub_release_clean(h, tier, slab, sub);
+    }
+    return OCM_OK;
+}
+
 int pool_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int rank, BlockRef *out) {
     if (tier < 0 || tier >= TIER_COUNT || !out) return OCM_EINVAL;
     PoolDesc &p = h->pool[tier];
     if (p.n_granules == 0) return OCM_ENOMEM;
     if (bytes == 0) bytes = 1;
     if (bytes > p.bytes) return OCM_ENOMEM;   // before any arithmetic: a huge size must not wrap to a small block
+    if (bytes <= p.granule / 2 && h->slabs_enabled.load(std::memory_order_relaxed) && slab_alloc(h, tier, bytes, pid, rank, out) == OCM_OK)
+        return OCM_OK;
+    int err = granule_alloc(h, tier, bytes, pid, rank, out, true);
+    // out of granules while empty slabs are being kept around for the next small request: give them back and retry
+    if (err == OCM_ENOMEM && slab_trim(h, tier)) err = granule_alloc(h, tier, bytes, pid, rank, out, true);
+    return err;
+}
+
+static int granule_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int rank, BlockRef *out, bool count) {
+    PoolDesc &p = h->pool[tier];
     const uint64_t n = (bytes + p.granule - 1) / p.granule;
     if (n == 0 || n > p.n_granules) return OCM_ENOMEM;
     std::atomic<uint64_t> *bm = table_bitmap(h, tier);
@@ -313,8 +514,10 @@ int pool_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int rank, Bloc
     r.signal_cpu.store(0, std::memory_order_relaxed);
     r.state.store(REGION_LIVE, std::memory_order_release);
     p.used_bytes.fetch_add(block_bytes, std::memory_order_relaxed);
-    p.live.fetch_add(1, std::memory_order_relaxed);
-    p.total_allocs.fetch_add(1, std::memory_order_relaxed);
+    if (count) {
+        p.live.fetch_add(1, std::memory_order_relaxed);
+        p.total_allocs.fetch_add(1, std::memory_order_relaxed);
+    }
     out->region = (uint32_t)start;
     out->generation = r.generation;
     out->offset = start * p.granule;
@@ -325,6 +528,7 @@ int pool_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int rank, Bloc
 
 int pool_free(TableHeader *h, int tier, uint32_t region, uint64_t id) {
     if (tier < 0 || tier >= TIER_COUNT) return OCM_EINVAL;
+    if (region_is_sub(region)) return sub_free(h, tier, region, id);
     PoolDesc &p = h->pool[tier];
     if (region >= p.n_granules) return OCM_EINVAL;
     Region *regs = table_regions(h, tier);
@@ -338,8 +542,10 @@ int pool_free(TableHeader *h, int tier, uint32_t region, uint64_t id) {
     sigext_release(h, r);
     const uint64_t block_bytes = (uint64_t)n * p.granule;
     p.used_bytes.fetch_sub(block_bytes, std::memory_order_relaxed);
-    p.live.fetch_sub(1, std::memory_order_relaxed);
-    p.total_frees.fetch_add(1, std::memory_order_relaxed);
+    if (r.owner_pid != kSlabOwnerPid) {   // the granule behind a slab was never counted as an allocation
+        p.live.fetch_sub(1, std::memory_order_relaxed);
+        p.total_frees.fetch_add(1, std::memory_order_relaxed);
+    }
     if (scrub) {
         p.dirty_bytes.fetch_add(block_bytes, std::memory_order_relaxed);
         stack_push(p.dirty_head, regs, region);
@@ -349,17 +555,21 @@ int pool_free(TableHeader *h, int tier, uint32_t region, uint64_t id) {
     return OCM_OK;
 }
 
+// Detach one dirty stack; returns its first element (index + 1) or 0.
+static uint32_t detach_stack(std::atomic<uint64_t> &head) {
+    uint64_t hd = head.load(std::memory_order_acquire);
+    for (;;) {
+        if (!head_idx(hd)) return 0;
+        if (head.compare_exchange_weak(hd, pack_head(head_tag(hd) + 1, 0), std::memory_order_acq_rel)) return head_idx(hd);
+    }
+}
+
 size_t pool_take_dirty(TableHeader *h, int tier, std::vector<DirtyBlock> *out) {
     PoolDesc &p = h->pool[tier];
     if (!p.n_granules) return 0;
     Region *regs = table_regions(h, tier);
-    uint64_t hd = p.dirty_head.load(std::memory_order_acquire);
-    for (;;) {
-        if (!head_idx(hd)) return 0;
-        if (p.dirty_head.compare_exchange_weak(hd, pack_head(head_tag(hd) + 1, 0), std::memory_order_acq_rel)) break;
-    }
     size_t n = 0;
-    for (uint32_t ip1 = head_idx(hd); ip1;) {
+    for (uint32_t ip1 = detach_stack(p.dirty_head); ip1;) {
         Region &r = regs[ip1 - 1];
         uint32_t nxt = r.next.load(std::memory_order_relaxed);
         r.state.store(REGION_SCRUBBING, std::memory_order_relaxed);
@@ -367,11 +577,33 @@ size_t pool_take_dirty(TableHeader *h, int tier, std::vector<DirtyBlock> *out) {
         ++n;
         ip1 = nxt;
     }
+    // released sub-blocks of slabs: same treatment, named by their sub-block reference
+    if (p.n_slabs) {
+        Region *subs = table_subs(h, tier);
+        for (uint32_t ip1 = detach_stack(p.sub_dirty_head); ip1;) {
+            Region &r = subs[ip1 - 1];
+            uint32_t nxt = r.next.load(std::memory_order_relaxed);
+            r.state.store(REGION_SCRUBBING, std::memory_order_relaxed);
+            const uint32_t slab = (ip1 - 1) / kSlabSubs, sub = (ip1 - 1) % kSlabSubs;
+            const uint32_t ref = kSlabFlag | (slab << 6) | sub;
+            out->push_back({ref, table_region_offset(h, tier, ref), p.granule >> (slab_class(slab) + 1)});
+            ++n;
+            ip1 = nxt;
+        }
+    }
     return n;
 }
 
 void pool_release_scrubbed(TableHeader *h, int tier, uint32_t region) {
     PoolDesc &p = h->pool[tier];
+    if (region_is_sub(region)) {
+        Region *sr = table_region_rec(h, tier, region);
+        if (!sr) return;
+        p.dirty_bytes.fetch_sub(p.granule >> (slab_class(sub_slab(region)) + 1), std::memory_order_relaxed);
+        sr->state.store(REGION_FREE, std::memory_order_release);
+        sub_release_clean(h, tier, sub_slab(region), sub_index(region));
+        return;
+    }
     Region &r = table_regions(h, tier)[region];
     const uint32_t n = r.n_granules;
     p.dirty_bytes.fetch_sub((uint64_t)n * p.granule, std::memory_order_relaxed);
@@ -383,11 +615,11 @@ uint64_t pool_scrub_host_inline(TableHeader *h, void *host_pool_base) {
     if (!host_pool_base) return 0;
     std::vector<DirtyBlock> blocks;
     if (!pool_take_dirty(h, TIER_HOST, &blocks)) return 0;
-    Region *regs = table_regions(h, TIER_HOST);
     uint64_t total = 0;
     for (auto &b : blocks) {
         // only the part the owner could touch needs clearing
-        uint64_t n = std::min<uint64_t>(b.bytes, (regs[b.region].bytes + 4095) & ~4095ull);
+        const Region *rec = table_region_rec(h, TIER_HOST, b.region);
+        uint64_t n = std::min<uint64_t>(b.bytes, ((rec ? rec->bytes : b.bytes) + 4095) & ~4095ull);
         memset(static_cast<char *>(host_pool_base) + b.offset, 0, n);
         total += b.bytes;
         pool_release_scrubbed(h, TIER_HOST, b.region);
@@ -420,6 +652,29 @@ size_t pool_reclaim(TableHeader *h, int tier, bool (*pred)(int, int, void *), vo
     PoolDesc &p = h->pool[tier];
     if (!p.n_granules) return 0;
     size_t n = 0;
+    // sub-blocks of active slabs first (their backing granules belong to nobody and stay)
+    {
+        Slab *slabs = table_slabs(h, tier);
+        Region *subs = table_subs(h, tier);
+        for (uint32_t s = 0; s < p.n_slabs; ++s) {
+            if (slabs[s].state.load(std::memory_order_acquire) != SLAB_ACTIVE) continue;
+            const uint32_t n_sub = class_subs(slab_class(s));
+            const uint64_t sub_size = p.granule >> (slab_class(s) + 1);
+            for (uint32_t k = 0; k < n_sub; ++k) {
+                Region &r = subs[(size_t)s * kSlabSubs + k];
+                if (r.state.load(std::memory_order_acquire) != REGION_LIVE || !pred(r.owner_pid, r.owner_rank, ctx)) continue;
+                const uint32_t ref = kSlabFlag | (s << 6) | k;
+                const uint64_t id = r.id;
+                BlockRef b;
+                b.region = ref; b.id = id; b.offset = table_region_offset(h, tier, ref); b.block_bytes = sub_size;
+                b.generation = r.generation;
+                if (pool_free(h, tier, ref, id) != OCM_OK) continue;
+                ++n;
+                if (bytes_out) *bytes_out += sub_size;
+                if (reclaimed) reclaimed->push_back(b);
+            }
+        }
+    }
     for_each_block(h, tier, [&](uint32_t i, Region &r) {
         if (r.state.load(std::memory_order_acquire) != REGION_LIVE || !pred(r.owner_pid, r.owner_rank, ctx)) return;
         const uint64_t id = r.id;
@@ -441,9 +696,51 @@ size_t pool_count_live(TableHeader *h, int tier) {
     if (!h->pool[tier].n_granules) return 0;
     size_t n = 0;
     for_each_block(h, tier, [&](uint32_t, Region &r) {
-        if (r.state.load(std::memory_order_acquire) == REGION_LIVE) ++n;
+        if (r.state.load(std::memory_order_acquire) == REGION_LIVE && r.owner_pid != kSlabOwnerPid) ++n;
     });
+    PoolDesc &p = h->pool[tier];
+    Slab *slabs = table_slabs(h, tier);
+    Region *subs = table_subs(h, tier);
+    for (uint32_t s = 0; s < p.n_slabs; ++s) {
+        if (slabs[s].state.load(std::memory_order_acquire) != SLAB_ACTIVE) continue;
+        for (uint32_t k = 0; k < class_subs(slab_class(s)); ++k)
+            if (subs[(size_t)s * kSlabSubs + k].state.load(std::memory_order_acquire) == REGION_LIVE) ++n;
+    }
     return n;
+}
+
+uint64_t pool_payload_bytes(TableHeader *h, int tier) {
+    PoolDesc &p = h->pool[tier];
+    uint64_t slab_granules = 0;
+    Slab *slabs = table_slabs(h, tier);
+    for (uint32_t s = 0; s < p.n_slabs; ++s)
+        if (slabs[s].state.load(std::memory_order_acquire) == SLAB_ACTIVE) ++slab_granules;
+    const uint64_t used = p.used_bytes.load(std::memory_order_acquire);
+    const uint64_t slab_bytes = slab_granules * p.granule;
+    return (used > slab_bytes ? used - slab_bytes : 0) + p.sub_bytes.load(std::memory_order_acquire);
+}
+
+int pool_audit(TableHeader *h, int tier, TableAudit *out) {
+    TableAudit a;
+    memset(&a, 0, sizeof a);
+    PoolDesc &p = h->pool[tier];
+    if (p.n_granules) {
+        std::atomic<uint64_t> *bm = table_bitmap(h, tier);
+        uint64_t bits = 0;
+        for (uint32_t w = 0; w < p.bitmap_words; ++w) bits += (uint64_t)__builtin_popcountll(bm[w].load(std::memory_order_acquire));
+        bits -= (uint64_t)p.bitmap_words * 64 - p.n_granules;          // the permanently-taken tail
+        a.bitmap_bytes = bits * p.granule;
+        a.used_bytes = p.used_bytes.load(std::memory_order_acquire);
+        a.dirty_bytes = p.dirty_bytes.load(std::memory_order_acquire);
+        a.live_records = pool_count_live(h, tier);
+        a.live_counter = p.live.load(std::memory_order_acquire);
+        // every taken granule is either in use or waiting to be zeroed (dirty sub-blocks sit inside used slabs)
+        if (a.bitmap_bytes < a.used_bytes || a.bitmap_bytes > a.used_bytes + a.dirty_bytes) ++a.problems;
+        if (a.live_records != a.live_counter) ++a.problems;
+        if (a.used_bytes > p.bytes) ++a.problems;
+    }
+    if (out) *out = a;
+    return a.problems;
 }
 
 int64_t mc_range_alloc(ClusterTable *c, uint64_t bytes, int owner_pid, int owner_rank) {

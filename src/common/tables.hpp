@@ -58,6 +58,33 @@ struct alignas(64) Region {
 };
 static_assert(sizeof(Region) == 64, "one cache line per region");
 
+// ---- slabs: size classes below the granule --------------------------------------------------------
+// A pool's granule grows with the pool (64 KiB for HBM pools up to 16 GiB, 1 MiB at 160 GiB), so a 4 KiB request
+// would burn a whole granule.  Requests of at most half a granule are therefore served from SLABS: one granule cut
+// into 2^k equal sub-blocks (k = 1..6, sub-blocks of at least 256 bytes), its free sub-blocks a 64-bit mask claimed
+// with compare-and-swap.  Slab i always serves class i % kSlabClasses, so a mask bit means the same thing in every
+// incarnation of slab i and a stale CAS can only ever claim a block that really is free.  Every sub-block has a
+// full Region record of its own (owner, id, generation, completion signals, share/attach state): it is an
+// allocation like any other, named by kSlabFlag | slab << 6 | sub wherever a granule index is expected.
+constexpr uint32_t kSlabFlag    = 0x80000000u;
+constexpr uint32_t kSlabSubs    = 64;
+constexpr uint32_t kSlabClasses = 6;       // class c: 2^(c+1) sub-blocks of granule >> (c+1) bytes
+constexpr uint32_t kMaxSlabs    = 1536;    // per tier: 256 slabs per class
+enum SlabState : uint32_t { SLAB_FREE = 0, SLAB_INIT = 1, SLAB_ACTIVE = 2, SLAB_RETIRING = 3 };
+struct alignas(64) Slab {
+    std::atomic<uint32_t> state;
+    uint32_t              region;       // backing granule (valid while ACTIVE)
+    uint64_t              backing_id;   // allocation id of the backing block
+    std::atomic<uint64_t> free_mask;    // bit s: sub-block s is free and clean
+    uint64_t              pad[5];
+};
+static_assert(sizeof(Slab) == 64, "one cache line per slab");
+inline bool     region_is_sub(uint32_t region) { return (region & kSlabFlag) != 0; }
+inline uint32_t sub_slab(uint32_t region) { return (region & ~kSlabFlag) >> 6; }
+inline uint32_t sub_index(uint32_t region) { return region & 63u; }
+inline uint32_t slab_class(uint32_t slab) { return slab % kSlabClasses; }
+inline uint32_t class_subs(uint32_t cls) { return 2u << cls; }
+
 // Completion counters of a block that is shared between applications (ocm_share / ocm_attach).
 // A system-scope reduction from a GPU to host memory is only atomic with respect to the SAME GPU on boxes
 // without PCIe atomics (cudaDevAttrHostNativeAtomicSupported = 0 on the B200 HGX boxes: four GPUs adding
@@ -90,6 +117,16 @@ struct PoolDesc {
     std::atomic<uint64_t> total_frees;
     std::atomic<uint64_t> dirty_head;    // {tag:32, idx+1:32}
     std::atomic<uint64_t> dirty_bytes;
+    // slabs (see above): headers, one Region per sub-block, their own dirty stack, free sub-blocks per class
+    uint64_t slabs_offset;               // Slab[n_slabs], from segment start
+    uint64_t subs_offset;                // Region[n_slabs * kSlabSubs]
+    uint32_t n_slabs;
+    uint32_t pad_slab;
+    std::atomic<uint64_t> sub_dirty_head;
+    std::atomic<uint64_t> sub_live;      // live sub-blocks
+    std::atomic<uint64_t> sub_bytes;     // bytes of live sub-blocks (their class size)
+    std::atomic<int64_t>  class_free[kSlabClasses];
+    std::atomic<uint32_t> class_hint[kSlabClasses];
 };
 
 enum GpuShareMode : uint32_t { GPU_SHARE_NONE = 0, GPU_SHARE_VMM_FD = 1, GPU_SHARE_CUDA_IPC = 2 };
@@ -108,6 +145,8 @@ struct TableHeader {
     uint64_t segment_bytes;
     std::atomic<uint32_t> ready;       // set last by the daemon
     std::atomic<uint32_t> scrub_enabled;
+    std::atomic<uint32_t> slabs_enabled;   // sub-granule size classes (OCM_NO_SLABS clears it)
+    uint32_t pad_hdr;
     std::atomic<uint64_t> next_id;
     std::atomic<uint64_t> heartbeat_ns; // daemon liveness (CLOCK_MONOTONIC)
     uint64_t mc_tail_offset;           // NVLS: byte offset inside the HBM pool mapping of the multicast slice
@@ -214,6 +253,27 @@ void table_format(void *base, size_t seg_bytes, int rank, int n_ranks, int daemo
 inline Region *table_regions(TableHeader *h, int tier) {
     return reinterpret_cast<Region *>(reinterpret_cast<char *>(h) + h->pool[tier].regions_offset);
 }
+inline Slab *table_slabs(TableHeader *h, int tier) {
+    return reinterpret_cast<Slab *>(reinterpret_cast<char *>(h) + h->pool[tier].slabs_offset);
+}
+inline Region *table_subs(TableHeader *h, int tier) {
+    return reinterpret_cast<Region *>(reinterpret_cast<char *>(h) + h->pool[tier].subs_offset);
+}
+// The record of a block named by a granule index or by a slab sub-block reference; nullptr when out of range.
+inline Region *table_region_rec(TableHeader *h, int tier, uint32_t region) {
+    const PoolDesc &p = h->pool[tier];
+    if (!region_is_sub(region)) return region < p.n_granules ? &table_regions(h, tier)[region] : nullptr;
+    const uint32_t s = sub_slab(region);
+    if (s >= p.n_slabs || sub_index(region) >= class_subs(slab_class(s))) return nullptr;
+    return &table_subs(h, tier)[(size_t)s * kSlabSubs + sub_index(region)];
+}
+// Byte offset of that block inside the pool (sub-blocks: only meaningful while their slab is active).
+inline uint64_t table_region_offset(TableHeader *h, int tier, uint32_t region) {
+    const PoolDesc &p = h->pool[tier];
+    if (!region_is_sub(region)) return (uint64_t)region * p.granule;
+    const uint32_t s = sub_slab(region);
+    return (uint64_t)table_slabs(h, tier)[s].region * p.granule + (uint64_t)sub_index(region) * (p.granule >> (slab_class(s) + 1));
+}
 bool table_validate(const TableHeader *h, size_t mapped_bytes);
 inline SigExt *table_sigext(TableHeader *h) {
     return reinterpret_cast<SigExt *>(reinterpret_cast<char *>(h) + h->sigext_offset);
@@ -255,8 +315,18 @@ inline bool pool_has_dirty(const TableHeader *h, int tier) {
 // to *bytes_out.
 size_t pool_reclaim(TableHeader *h, int tier, bool (*pred)(int pid, int rank, void *ctx), void *ctx,
                     uint64_t *bytes_out, std::vector<BlockRef> *reclaimed = nullptr);
-// Count LIVE blocks (O(blocks)); consistency checks for tests.
+// Count LIVE blocks (O(blocks)); consistency checks for tests.  Sub-blocks count, the granules backing slabs do not.
 size_t pool_count_live(TableHeader *h, int tier);
+// Bytes of granules in use as seen by applications: used_bytes without the free remainder of active slabs.
+uint64_t pool_payload_bytes(TableHeader *h, int tier);
+// Daemon-side audit: do the counters still agree with the bitmap and the records?  Transient disagreement is
+// normal while other processes allocate; a caller that sees the same non-zero result twice with unchanged
+// total_allocs/total_frees has found a corrupted table (a misbehaving client).  Returns the number of problems.
+struct TableAudit {
+    uint64_t bitmap_bytes, used_bytes, dirty_bytes, live_records, live_counter;
+    int problems;
+};
+int pool_audit(TableHeader *h, int tier, TableAudit *out);
 
 // ---- cluster table / governor primitives -----------------------------------
 void cluster_format(ClusterTable *c, int n_ranks);

@@ -169,6 +169,7 @@ int Daemon::setup_pools() {
     tbl_->mc_bytes = mc_bytes_;
     if (gpu_ >= 0) gpu::get_uuid(gpu_, tbl_->gpu_uuid);
     if (getenv("OCM_NO_SCRUB")) tbl_->scrub_enabled.store(0);
+    if (getenv("OCM_NO_SLABS")) tbl_->slabs_enabled.store(0);
 
     if (host_bytes) {
         if (!shm_create(shm_host_pool_name(rank_), tbl_->pool[TIER_HOST].bytes, true, &host_map_, &err)) {
@@ -781,7 +782,7 @@ void Daemon::fill_stats(StatsPayload *s) {
     for (int t = 0; t < TIER_COUNT; ++t) {
         PoolDesc &p = tbl_->pool[t];
         s->pool_bytes[t] = p.bytes;
-        s->pool_used[t] = p.used_bytes.load(std::memory_order_relaxed);
+        s->pool_used[t] = pool_payload_bytes(tbl_, t);   // what applications hold (empty cached slabs are free space)
         s->allocs_live += p.live.load(std::memory_order_relaxed);
         s->allocs_total += p.total_allocs.load(std::memory_order_relaxed);
         s->frees_total += p.total_frees.load(std::memory_order_relaxed);
@@ -791,6 +792,7 @@ void Daemon::fill_stats(StatsPayload *s) {
     s->msgs_out = msgs_out_.load();
     s->reclaimed_regions = reclaimed_.load();
     s->scrubbed_bytes = scrubbed_bytes_.load();
+    s->table_faults = table_faults_.load();
 }
 
 // ------------------------------------------------------------ NVLS bring-up --
@@ -934,8 +936,8 @@ void Daemon::reclaim_dead() {
         if (!n) continue;
         reclaimed_.fetch_add(n);
         LOGI("reclaimed %zu block(s), %llu bytes in tier %d from dead owners", n, (unsigned long long)bytes, t);
-        Region *regs = table_regions(tbl_, t);
-        for (auto &b : got) note_free(rank_, t, regs[b.region].bytes);
+        for (auto &b : got)
+            if (const Region *rec = table_region_rec(tbl_, t, b.region)) note_free(rank_, t, rec->bytes);
     }
     // multicast ranges of this rank's dead applications: mark them; every daemon's scrubber zeroes its own slice
     if (mc_bytes_ && gpu_ >= 0) {
@@ -989,9 +991,43 @@ void Daemon::on_timer() {
         }
     }
     mc_step();
+    if (now - last_audit_ns_ > 1000ull * 1000000ull) {
+        last_audit_ns_ = now;
+        audit_tables();
+    }
     if (now - last_reclaim_ns_ > 250ull * 1000000ull) {
         last_reclaim_ns_ = now;
         reclaim_dead();
+    }
+}
+
+// Every attached process can CAS this rank's tables (that is what makes ocm_alloc a handful of atomics), so a buggy
+// client could leave them inconsistent.  Once a second the daemon checks that the bitmap, the byte counters and the
+// records still tell the same story.  A disagreement only counts when it shows twice in a row with no allocation or
+// release in between (other processes are allowed to be in the middle of an operation); it is logged and exported
+// through MSG_STATS (table_faults) - the daemon does not try to repair a table somebody else scribbled on.
+void Daemon::audit_tables() {
+    for (int t = 0; t < TIER_COUNT; ++t) {
+        PoolDesc &p = tbl_->pool[t];
+        if (!p.n_granules) continue;
+        const uint64_t ops_before = p.total_allocs.load() + p.total_frees.load();
+        const uint64_t dirty_before = p.dirty_bytes.load();
+        TableAudit a;
+        const int problems = pool_audit(tbl_, t, &a);
+        const bool quiet = ops_before == p.total_allocs.load() + p.total_frees.load() && dirty_before == p.dirty_bytes.load();
+        if (!problems || !quiet) {
+            audit_suspect_[t] = 0;
+            continue;
+        }
+        if (audit_suspect_[t] == ops_before + 1) {   // the same picture as a second ago: nobody is in the middle of anything
+            table_faults_.fetch_add(1);
+            LOGE("tier %d tables are inconsistent: bitmap %llu B, used %llu B, dirty %llu B, live records %llu, live counter %llu",
+                 t, (unsigned long long)a.bitmap_bytes, (unsigned long long)a.used_bytes, (unsigned long long)a.dirty_bytes,
+                 (unsigned long long)a.live_records, (unsigned long long)a.live_counter);
+            audit_suspect_[t] = 0;
+        } else {
+            audit_suspect_[t] = ops_before + 1;
+        }
     }
 }
 
@@ -1022,10 +1058,10 @@ void Daemon::scrub_loop() {
                         ocmk::launch_fill((char *)gpu_pool_.ptr + b.offset, b.bytes, 0, (cudaStream_t)scrub_stream_);
                     cudaStreamSynchronize((cudaStream_t)scrub_stream_);
                 } else if (t == TIER_HOST && host_map_.base) {
-                    Region *regs = table_regions(tbl_, t);
                     for (auto &b : blocks) {
                         // only the part the owner could touch needs clearing
-                        uint64_t n = std::min<uint64_t>(b.bytes, (regs[b.region].bytes + 4095) & ~4095ull);
+                        const Region *rec = table_region_rec(tbl_, t, b.region);
+                        uint64_t n = std::min<uint64_t>(b.bytes, ((rec ? rec->bytes : b.bytes) + 4095) & ~4095ull);
                         memset((char *)host_map_.base + b.offset, 0, n);
                     }
                 }

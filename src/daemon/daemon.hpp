@@ -86,6 +86,7 @@ class Daemon {
     void close_peer(int fd);
     void scrub_loop();
     void reclaim_dead();
+    void audit_tables();
     void mc_step();                           // NVLS multicast bring-up state machine (timer driven)
     ClusterTable *shared_cluster();           // rank 0: own table; others: lazily mapped
     uint32_t next_seq() { return ++seq_ ? seq_ : ++seq_; }
@@ -109,7 +110,9 @@ class Daemon {
     std::map<uint32_t, Pending> pending_;
     uint32_t seq_ = 0;
     bool joined_ = false;
-    uint64_t join_deadline_ns_ = 0, last_join_try_ns_ = 0, last_reclaim_ns_ = 0;
+    uint64_t join_deadline_ns_ = 0, last_join_try_ns_ = 0, last_reclaim_ns_ = 0, last_audit_ns_ = 0;
+    uint64_t audit_suspect_[TIER_COUNT] = {0, 0};   // operation count + 1 at which an audit last disagreed (0: none)
+    std::atomic<uint64_t> table_faults_{0};
     std::atomic<bool> stop_{false};
     std::thread scrubber_;
     // counters

@@ -539,8 +539,54 @@ template <> struct ElemIO<DT_F8E4M3> {
     }
 };
 
+// Store the 32 converted elements of every lane so that each store instruction of the warp writes consecutive
+// 32-byte pieces.  A lane's chunk is KB = 128 (fp32) or 64 (bf16) bytes of destination: storing it directly would
+// put the lanes of one instruction KB bytes apart, i.e. a quarter (half) of every 128-byte line per instruction -
+// harmless inside one HBM, where the L2 merges the sectors, but peer writes bypass the L2 and go out over NVLink as
+// partial-line packets (measured 371 GB/s for an fp32 -> bf16 put against 660+ for full lines).  So the warp
+// transposes through shared memory: rows of KB bytes with a 16-byte pad (conflict-free 128-bit accesses), read back
+// as the warp-contiguous 32-byte piece q * 1 KiB + lane * 32 whose owner lane supplies the destination address.
+template <int DDT> struct WideStore {
+    static constexpr int KB = ElemIO<DDT>::kBytes;
+    static constexpr int kPitch = KB + 16;
+    static constexpr int kWarpBytes = 32 * kPitch;
+    static __device__ __forceinline__ void run(uint8_t *w, uint32_t lane, const float (&v)[32], uint8_t *my_dst) {
+        uint32_t words[KB / 4];
+        if (DDT == DT_F32) {
+#pragma unroll
+            for (int k = 0; k < 32; ++k) words[k % (KB / 4)] = __float_as_uint(v[k]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 16; ++k) words[k % (KB / 4)] = pack_bf16x2(v[2 * k], v[2 * k + 1]);
+        }
+        uint8_t *row = w + lane * kPitch;
+#pragma unroll
+        for (int j = 0; j < KB / 16; ++j)
+            *reinterpret_cast<uint4 *>(row + 16 * j) = make_uint4(words[4 * j], words[4 * j + 1], words[4 * j + 2], words[4 * j + 3]);
+        __syncwarp();
+        const uint64_t base = reinterpret_cast<uint64_t>(my_dst);
+#pragma unroll
+        for (int q = 0; q < KB / 32; ++q) {
+            const uint32_t x = (uint32_t)q * 1024u + lane * 32u;
+            const uint32_t j = x / KB, off = x % KB;
+            const uint64_t bj = __shfl_sync(0xffffffffu, base, (int)j);
+            const uint4 lo = *reinterpret_cast<const uint4 *>(w + j * kPitch + off);
+            const uint4 hi = *reinterpret_cast<const uint4 *>(w + j * kPitch + off + 16);
+            if (bj) {
+                W32 o;
+                o.w[0] = lo.x; o.w[1] = lo.y; o.w[2] = lo.z; o.w[3] = lo.w;
+                o.w[4] = hi.x; o.w[5] = hi.y; o.w[6] = hi.z; o.w[7] = hi.w;
+                WideVec<32>::st(reinterpret_cast<uint8_t *>(bj) + off, o);
+            }
+        }
+        __syncwarp();
+    }
+};
+
 template <int SDT, int DDT, int U>
 __global__ void __launch_bounds__(256, 2) ocm_cast32_kernel(CastArgs a) {
+    constexpr bool wide_dst = DDT != DT_F8E4M3;
+    __shared__ __align__(16) uint8_t xpose[wide_dst ? 8 * (32 * (ElemIO<wide_dst ? DDT : DT_F32>::kBytes + 16)) : 16];
     constexpr bool quant = DDT == DT_F8E4M3, dequant = SDT == DT_F8E4M3;
     const uint32_t G = a.blk == 128 ? 4u : 1u;                  // threads per scale block
     const uint64_t cpr = a.elems / 32;                          // chunks per row (host guarantees whole chunks)
@@ -587,7 +633,12 @@ __global__ void __launch_bounds__(256, 2) ocm_cast32_kernel(CastArgs a) {
 #pragma unroll
                 for (int k = 0; k < 32; ++k) v[i][k] = __fmul_rn(v[i][k], scale);
             }
-            if (valid[i]) ElemIO<DDT>::store(a.dst + dof[i] + (int64_t)(ch[i] * ElemIO<DDT>::kBytes), v[i]);
+            uint8_t *my_dst = valid[i] ? a.dst + dof[i] + (int64_t)(ch[i] * ElemIO<DDT>::kBytes) : nullptr;
+            if constexpr (wide_dst) {
+                WideStore<DDT>::run(xpose + (threadIdx.x >> 5) * WideStore<DDT>::kWarpBytes, (uint32_t)lane, v[i], my_dst);
+            } else {
+                if (my_dst) ElemIO<DDT>::store(my_dst, v[i]);
+            }
         }
     }
     __syncthreads();

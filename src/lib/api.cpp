@@ -69,43 +69,74 @@ unsigned *next_ticket() {
     return c.tickets + (c.ticket_cursor.fetch_add(1, std::memory_order_relaxed) % kNumTickets);
 }
 
+// One request/reply exchange with the local daemon.  Several threads may have exchanges in flight at once: each
+// registers its sequence number, and whichever waiter currently holds the "receiver" role reads the process' one
+// mailbox and hands every reply to the thread that waits for that sequence number (the reference serialises the
+// whole round trip behind one blocking receive, reference src/lib.c:214-220; so did round 1 of this library).
 int daemon_call(Message &m, int timeout_ms) {
     Ctx &c = ctx();
-    std::lock_guard<std::mutex> g(c.mq_mu);
-    m.pid = (int)getpid();
-    m.seq = ++c.seq;
-    uint16_t want_type = m.type == MSG_CONNECT ? (uint16_t)MSG_CONNECT_CONFIRM
-                         : (m.type == MSG_STATS || m.type == MSG_PING) ? m.type : (uint16_t)MSG_RELEASE_APP;
-    int r = c.box.send(c.daemon_mq, &m, timeout_ms);
-    if (r) {
-        LOGW("send to daemon failed: %s", strerror(-r));
-        return OCM_ENODAEMON;
+    Ctx::PendingReply slot;
+    slot.want_type = m.type == MSG_CONNECT ? (uint16_t)MSG_CONNECT_CONFIRM
+                     : (m.type == MSG_STATS || m.type == MSG_PING) ? m.type : (uint16_t)MSG_RELEASE_APP;
+    uint32_t seq;
+    {
+        std::lock_guard<std::mutex> g(c.mq_mu);
+        m.pid = (int)getpid();
+        m.seq = seq = ++c.seq;
+        c.mq_pending[seq] = &slot;
+        int r = c.box.send(c.daemon_mq, &m, timeout_ms);
+        if (r) {
+            c.mq_pending.erase(seq);
+            LOGW("send to daemon failed: %s", strerror(-r));
+            return OCM_ENODAEMON;
+        }
     }
-    uint64_t deadline = mono_ns() + (uint64_t)timeout_ms * 1000000ull;
+    const uint64_t deadline = mono_ns() + (uint64_t)timeout_ms * 1000000ull;
+    std::unique_lock<std::mutex> lk(c.mq_mu);
+    auto leave = [&](int err) {
+        c.mq_pending.erase(seq);
+        c.mq_cv.notify_all();
+        return err;
+    };
     for (;;) {
-        int64_t left = (int64_t)(deadline - mono_ns()) / 1000000;
-        if (left <= 0) return OCM_ENODAEMON;
+        if (slot.ready) {
+            m = slot.rep;
+            return leave(slot.rep.err);
+        }
+        const int64_t left = (int64_t)(deadline - mono_ns()) / 1000000;
+        if (left <= 0) return leave(OCM_ENODAEMON);
+        if (c.mq_receiving) {   // somebody else is reading the mailbox: it wakes us when our reply is in (or it leaves)
+            c.mq_cv.wait_for(lk, std::chrono::milliseconds(std::min<int64_t>(left, 20)));
+            continue;
+        }
+        c.mq_receiving = true;
+        lk.unlock();
         Message rep;
-        r = c.box.recv(&rep, (int)std::min<int64_t>(left, 200));
-        if (r < 0) return OCM_ENODAEMON;
+        int r = c.box.recv(&rep, (int)std::min<int64_t>(left, 50));
+        bool dead = r < 0;
         if (r == 0) {
             // detect a dead daemon instead of waiting out the timeout
-            if (c.daemon_pid > 0 && kill(c.daemon_pid, 0) != 0 && errno == ESRCH) return OCM_ENODAEMON;
+            if (c.daemon_pid > 0 && kill(c.daemon_pid, 0) != 0 && errno == ESRCH) dead = true;
             // a killed-but-unreaped daemon still has a pid: its heartbeat (20 ms period) tells the truth
             const TableHeader *hb = c.view[c.rank].hdr;
             if (hb) {
                 uint64_t beat = hb->heartbeat_ns.load(std::memory_order_relaxed);
-                if (beat && mono_ns() > beat + 1500000000ull) return OCM_ENODAEMON;
+                if (beat && mono_ns() > beat + 1500000000ull) dead = true;
             }
-            continue;
         }
-        if (!rep.valid() || rep.seq != m.seq || rep.type != want_type) {
-            LOGW("unexpected reply %s seq %u (want %s seq %u) ignored", msg_type_str(rep.type), rep.seq,
-                 msg_type_str(want_type), m.seq);
-            continue;
+        lk.lock();
+        c.mq_receiving = false;
+        if (dead) return leave(OCM_ENODAEMON);
+        if (r == 1) {
+            auto it = rep.valid() ? c.mq_pending.find(rep.seq) : c.mq_pending.end();
+            if (it != c.mq_pending.end() && rep.type == it->second->want_type) {
+                it->second->rep = rep;
+                it->second->ready = true;
+            } else {
+                LOGW("unexpected reply %s seq %u ignored", msg_type_str(rep.type), rep.seq);
+            }
         }
-        m = rep;
-        return rep.err;
+        c.mq_cv.notify_all();
     }
 }
 
@@ -289,7 +320,7 @@ static int alloc_side(uint32_t type, uint64_t bytes, int policy, int explicit_ra
     out->offset = a.offset;
     out->bytes = bytes;
     out->ptr = v ? side_ptr(v, (int)a.tier, a.offset) : nullptr;
-    out->rec = v ? &table_regions(v->hdr, (int)a.tier)[a.region] : nullptr;
+    out->rec = v ? table_region_rec(v->hdr, (int)a.tier, a.region) : nullptr;
     out->hdr = v ? v->hdr : nullptr;
     out->sig_gpu = out->rec ? &out->rec->signal : nullptr;
     out->sig_cpu = out->rec ? &out->rec->signal_cpu : nullptr;
@@ -878,15 +909,16 @@ int ocm_attach(const struct ocm_share_token *tok, ocm_alloc_t *out) {
     if (tok->tier == TIER_GPU && c.device < 0) return -OCM_ENOGPU;
     RankView *v = get_view(tok->rank, tok->tier == TIER_GPU);
     if (!v) return -OCM_ENODAEMON;
-    const PoolDesc &pd = v->hdr->pool[tok->tier];
-    if (tok->region >= pd.n_granules) return -OCM_EINVAL;
-    Region *rec = &table_regions(v->hdr, (int)tok->tier)[tok->region];
+    Region *rec = table_region_rec(v->hdr, (int)tok->tier, tok->region);
+    if (!rec) return -OCM_EINVAL;
     // count ourselves in first, then check that the block is (still) the one the token names
     rec->attached.fetch_add(1, std::memory_order_acq_rel);
     const uint32_t ext = rec->ext.load(std::memory_order_acquire);
     const bool live = rec->state.load(std::memory_order_acquire) == REGION_LIVE && rec->id == tok->id &&
                       rec->generation == tok->generation && rec->bytes == tok->bytes && ext && ext <= v->hdr->n_sigext;
-    void *ptr = live ? side_ptr(v, (int)tok->tier, (uint64_t)tok->region * pd.granule) : nullptr;
+    // (a sub-block's offset is read after the liveness check: its slab cannot retire while the block is live)
+    const uint64_t blk_off = live ? table_region_offset(v->hdr, (int)tok->tier, tok->region) : 0;
+    void *ptr = live ? side_ptr(v, (int)tok->tier, blk_off) : nullptr;
     if (!ptr) {
         attached_dec(rec);
         return live ? (tok->tier == TIER_GPU ? -OCM_ENOGPU : -OCM_ENODAEMON) : -OCM_ESTALE;
@@ -907,7 +939,7 @@ int ocm_attach(const struct ocm_share_token *tok, ocm_alloc_t *out) {
     s.region = tok->region;
     s.generation = tok->generation;
     s.id = tok->id;
-    s.offset = (uint64_t)tok->region * pd.granule;
+    s.offset = blk_off;
     s.bytes = tok->bytes;
     s.ptr = ptr;
     s.rec = rec;
@@ -947,9 +979,9 @@ int ocm_get_stats(struct ocm_stats *out) {
     out->slow_path_allocs = c.n_slow.load();
     if (RankView *v = get_view(c.rank, false)) {
         out->pool_gpu_bytes = v->hdr->pool[TIER_GPU].bytes;
-        out->pool_gpu_used = v->hdr->pool[TIER_GPU].used_bytes.load();
+        out->pool_gpu_used = pool_payload_bytes(v->hdr, TIER_GPU);
         out->pool_host_bytes = v->hdr->pool[TIER_HOST].bytes;
-        out->pool_host_used = v->hdr->pool[TIER_HOST].used_bytes.load();
+        out->pool_host_used = pool_payload_bytes(v->hdr, TIER_HOST);
     }
     return 0;
 }

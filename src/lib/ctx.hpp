@@ -8,6 +8,8 @@
 #include "../kernels/kernels.h"
 #include "../../include/oncillamem.h"
 #include <atomic>
+#include <condition_variable>
+#include <unordered_map>
 #include <mutex>
 #include <unordered_set>
 #include <vector>
@@ -108,7 +110,17 @@ namespace ocm {
 
 struct Ctx {
     std::mutex   mu;             // init/tini + allocation set
-    std::mutex   mq_mu;          // one request/reply exchange at a time
+    // Daemon exchanges: mq_mu guards the sequence counter, the table of waiting threads and the "receiver" role
+    // (the one waiter that currently reads the mailbox and distributes replies by sequence number).
+    struct PendingReply {
+        Message  rep;
+        uint16_t want_type = 0;
+        bool     ready = false;
+    };
+    std::mutex   mq_mu;
+    std::condition_variable mq_cv;
+    std::unordered_map<uint32_t, PendingReply *> mq_pending;
+    bool         mq_receiving = false;
     bool         inited = false;
     int          rank = 0, n_ranks = 1;
     int          daemon_pid = -1;

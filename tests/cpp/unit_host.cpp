@@ -1,5 +1,5 @@
 // Native unit tests of the host substrate (no daemon, no GPU needed):
-//   unit_host <suite>|all     suites: msg nodefile ring tables tables_mt governor topo pmsg sock oracle
+//   unit_host <suite>|all     suites: msg nodefile ring tables tables_mt slabs governor topo pmsg sock oracle
 // The reference has no unit layer at all; these are new.
 #include "common/governor.hpp"
 #include "common/msg.hpp"
@@ -155,6 +155,7 @@ static TableHeader *fresh_table(std::vector<char> &buf, uint64_t gpu, uint64_t h
 static void t_tables() {
     std::vector<char> buf;
     TableHeader *h = fresh_table(buf, 64ull << 20, 1ull << 20); // 1024 GPU granules of 64 KiB, 256 host granules
+    h->slabs_enabled.store(0);   // this suite is about whole granules; t_slabs covers the size classes below them
     CHECK(h->pool[TIER_GPU].granule == 65536 && h->pool[TIER_GPU].n_granules == 1024);
     CHECK(h->pool[TIER_HOST].granule == 4096 && h->pool[TIER_HOST].n_granules == 256);
     CHECK(default_granule(160ull << 30, TIER_GPU) == (1ull << 20)); // 160 GiB pool -> <= 2^18 granules
@@ -224,6 +225,149 @@ static void t_tables() {
     BlockRef hb3;
     CHECK(pool_alloc(h, TIER_HOST, 100, 1, 0, &hb3) == OCM_OK);
     CHECK(sigext_claim(h, TIER_HOST, hb3.region) == x && x->slot[1].load() == 0);   // reused, counters cleared
+}
+
+// Size classes below the granule (tables.hpp, "slabs"): small requests share a granule, every sub-block is an
+// allocation of its own (record, id, signals, share), released blocks are zeroed before reuse, empty slabs go back.
+static void t_slabs() {
+    std::vector<char> buf;
+    TableHeader *h = fresh_table(buf, 64ull << 20, 1ull << 20);
+    PoolDesc &p = h->pool[TIER_GPU];
+    CHECK(p.n_slabs > 0 && p.n_slabs % kSlabClasses == 0 && h->slabs_enabled.load() == 1);
+    // 100 x 4 KiB: 16 per 64 KiB granule -> 7 granules instead of 100
+    std::vector<BlockRef> small;
+    std::set<uint64_t> offs;
+    for (int i = 0; i < 100; ++i) {
+        BlockRef b;
+        CHECK(pool_alloc(h, TIER_GPU, 4096, 21, 0, &b) == OCM_OK);
+        CHECK(region_is_sub(b.region) && b.block_bytes == 4096 && b.offset % 4096 == 0 && offs.insert(b.offset).second);
+        Region *r = table_region_rec(h, TIER_GPU, b.region);
+        CHECK(r && r->state.load() == REGION_LIVE && r->owner_pid == 21 && r->bytes == 4096 && r->id == b.id);
+        CHECK(table_region_offset(h, TIER_GPU, b.region) == b.offset);
+        small.push_back(b);
+    }
+    CHECK(p.used_bytes.load() == 7 * 65536ull && p.live.load() == 100 && pool_count_live(h, TIER_GPU) == 100);
+    CHECK(pool_payload_bytes(h, TIER_GPU) == 100 * 4096ull);
+    TableAudit au;
+    CHECK(pool_audit(h, TIER_GPU, &au) == 0 && au.live_records == 100);
+    // other classes: 1000 B -> 1 KiB blocks, 20 KiB -> 32 KiB blocks; more than half a granule takes granules
+    BlockRef k1, k20, k33;
+    CHECK(pool_alloc(h, TIER_GPU, 1000, 21, 0, &k1) == OCM_OK && region_is_sub(k1.region) && k1.block_bytes == 1024);
+    CHECK(pool_alloc(h, TIER_GPU, 20 << 10, 21, 0, &k20) == OCM_OK && region_is_sub(k20.region) && k20.block_bytes == 32768);
+    CHECK(pool_alloc(h, TIER_GPU, 33 << 10, 21, 0, &k33) == OCM_OK && !region_is_sub(k33.region) && k33.block_bytes == 65536);
+    CHECK(slab_class(sub_slab(k1.region)) == 5 && slab_class(sub_slab(k20.region)) == 0);
+    // release: double free and wrong id are refused; the block is zeroed (dirty -> scrubbing -> free) before reuse
+    BlockRef v = small[37];
+    CHECK(pool_free(h, TIER_GPU, v.region, v.id + 1) == OCM_ESTALE);
+    CHECK(pool_free(h, TIER_GPU, v.region, v.id) == OCM_OK);
+    CHECK(pool_free(h, TIER_GPU, v.region, v.id) == OCM_ESTALE);
+    CHECK(table_region_rec(h, TIER_GPU, v.region)->state.load() == REGION_DIRTY && pool_has_dirty(h, TIER_GPU));
+    BlockRef w;
+    CHECK(pool_alloc(h, TIER_GPU, 4096, 22, 0, &w) == OCM_OK && w.offset != v.offset);   // not handed out while dirty
+    std::vector<DirtyBlock> dirty;
+    CHECK(pool_take_dirty(h, TIER_GPU, &dirty) == 1 && dirty[0].region == v.region && dirty[0].offset == v.offset && dirty[0].bytes == 4096);
+    pool_release_scrubbed(h, TIER_GPU, v.region);
+    CHECK(!pool_has_dirty(h, TIER_GPU) && table_region_rec(h, TIER_GPU, v.region)->state.load() == REGION_FREE);
+    BlockRef again;
+    bool reused = false;
+    std::vector<BlockRef> extra;
+    for (int i = 0; i < 20 && !reused; ++i) {
+        CHECK(pool_alloc(h, TIER_GPU, 4096, 22, 0, &again) == OCM_OK);
+        reused = again.offset == v.offset;
+        extra.push_back(again);
+    }
+    CHECK(reused && again.generation == v.generation + 1 && again.id != v.id);
+    // a sub-block is a full allocation: completion counters and the share extension work on it
+    Region *wr = table_region_rec(h, TIER_GPU, w.region);
+    SigExt *x = sigext_claim(h, TIER_GPU, w.region);
+    CHECK(x && wr->ext.load() != 0 && x->id == w.id);
+    wr->signal.fetch_add(3);
+    x->slot[2].fetch_add(4);
+    CHECK(region_signal_total(h, *wr) == 7);
+    CHECK(pool_free(h, TIER_GPU, w.region, w.id) == OCM_OK && x->owner.load() == 0);
+    // dead owners: sub-blocks are reclaimed like granule blocks; the granules behind slabs belong to nobody
+    uint64_t bytes = 0;
+    std::vector<BlockRef> got;
+    auto pred = [](int pid, int, void *) { return pid == 21; };
+    const size_t n21 = 99 + 3;       // the 4 KiB blocks still held by pid 21, k1, k20, k33
+    CHECK(pool_reclaim(h, TIER_GPU, pred, nullptr, &bytes, &got) == n21 && got.size() == n21);
+    CHECK(bytes == 99 * 4096ull + 1024 + 32768 + 65536);
+    // everything released and scrubbed: the slabs retire (one per class may stay cached), the audit still agrees
+    for (auto &b : extra) CHECK(pool_free(h, TIER_GPU, b.region, b.id) == OCM_OK);
+    for (int round = 0; round < 4; ++round) {
+        dirty.clear();
+        pool_take_dirty(h, TIER_GPU, &dirty);
+        for (auto &d : dirty) pool_release_scrubbed(h, TIER_GPU, d.region);
+    }
+    CHECK(pool_count_live(h, TIER_GPU) == 0 && p.live.load() == 0 && p.sub_live.load() == 0 && p.sub_bytes.load() == 0);
+    CHECK(p.used_bytes.load() <= 3 * 65536ull && !pool_has_dirty(h, TIER_GPU));
+    CHECK(pool_audit(h, TIER_GPU, &au) == 0);
+    // a request for the whole pool makes the allocator give the cached empty slabs back (they are zeroed first)
+    BlockRef whole;
+    CHECK(pool_alloc(h, TIER_GPU, p.bytes, 30, 0, &whole) == OCM_ENOMEM && pool_has_dirty(h, TIER_GPU));
+    dirty.clear();
+    pool_take_dirty(h, TIER_GPU, &dirty);
+    for (auto &d : dirty) pool_release_scrubbed(h, TIER_GPU, d.region);
+    CHECK(p.used_bytes.load() == 0);
+    CHECK(pool_alloc(h, TIER_GPU, p.bytes, 30, 0, &whole) == OCM_OK && pool_free(h, TIER_GPU, whole.region, whole.id) == OCM_OK);
+    dirty.clear();
+    pool_take_dirty(h, TIER_GPU, &dirty);
+    for (auto &d : dirty) pool_release_scrubbed(h, TIER_GPU, d.region);
+    p.used_bytes.fetch_add(5 * 65536ull);      // what a misbehaving client could do
+    CHECK(pool_audit(h, TIER_GPU, &au) > 0);
+    p.used_bytes.fetch_sub(5 * 65536ull);
+    // slabs off: the same request takes a whole granule again
+    h->slabs_enabled.store(0);
+    CHECK(pool_alloc(h, TIER_GPU, 4096, 23, 0, &w) == OCM_OK && !region_is_sub(w.region) && w.block_bytes == 65536);
+    h->slabs_enabled.store(1);
+    // host tier: 4 KiB granules -> 256-byte .. 2 KiB classes
+    BlockRef hb;
+    CHECK(pool_alloc(h, TIER_HOST, 200, 1, 0, &hb) == OCM_OK && region_is_sub(hb.region) && hb.block_bytes == 256);
+    CHECK(pool_alloc(h, TIER_HOST, 3000, 1, 0, &hb) == OCM_OK && !region_is_sub(hb.region) && hb.block_bytes == 4096);
+
+    // concurrent small allocations and releases from 8 threads: no byte handed out twice, nothing leaks
+    std::vector<char> buf2;
+    TableHeader *g = fresh_table(buf2, 32ull << 20, 0);
+    g->scrub_enabled.store(0);
+    const int T = 8, ITER = 20000;
+    std::vector<std::atomic<int>> owner((32ull << 20) / 1024);
+    for (auto &o : owner) o.store(0);
+    std::atomic<int> errors{0};
+    std::vector<std::thread> th;
+    for (int t = 0; t < T; ++t)
+        th.emplace_back([&, t] {
+            std::vector<BlockRef> mine;
+            uint64_t rng = 0x9E3779B97F4A7C15ull * (t + 1);
+            for (int i = 0; i < ITER; ++i) {
+                rng ^= rng << 13; rng ^= rng >> 7; rng ^= rng << 17;
+                if (mine.size() < 24 && (rng & 1)) {
+                    static const uint64_t sizes[] = {700, 1024, 3000, 4096, 9000, 16384, 30000, 70000};
+                    BlockRef b;
+                    if (pool_alloc(g, TIER_GPU, sizes[(rng >> 8) % 8], 100 + t, 0, &b) == OCM_OK) {
+                        for (uint64_t k = b.offset / 1024; k < (b.offset + b.block_bytes) / 1024; ++k)
+                            if (owner[k].exchange(t + 1) != 0) errors++;
+                        mine.push_back(b);
+                    }
+                } else if (!mine.empty()) {
+                    const size_t pick = (rng >> 16) % mine.size();
+                    BlockRef b = mine[pick];
+                    mine.erase(mine.begin() + pick);
+                    for (uint64_t k = b.offset / 1024; k < (b.offset + b.block_bytes) / 1024; ++k)
+                        if (owner[k].exchange(0) != t + 1) errors++;
+                    if (pool_free(g, TIER_GPU, b.region, b.id) != OCM_OK) errors++;
+                }
+            }
+            for (auto &b : mine) {
+                for (uint64_t k = b.offset / 1024; k < (b.offset + b.block_bytes) / 1024; ++k)
+                    if (owner[k].exchange(0) != t + 1) errors++;
+                if (pool_free(g, TIER_GPU, b.region, b.id) != OCM_OK) errors++;
+            }
+        });
+    for (auto &t : th) t.join();
+    CHECK(errors.load() == 0);
+    CHECK(pool_count_live(g, TIER_GPU) == 0 && g->pool[TIER_GPU].live.load() == 0 && g->pool[TIER_GPU].sub_bytes.load() == 0);
+    CHECK(pool_audit(g, TIER_GPU, &au) == 0);
+    CHECK(g->pool[TIER_GPU].used_bytes.load() <= (uint64_t)kSlabClasses * 2 * 65536);   // at most the cached slabs remain
 }
 
 static void t_tables_mt() {
@@ -610,7 +754,7 @@ static void t_oracle() {
 int main(int argc, char **argv) {
     std::string which = argc > 1 ? argv[1] : "all";
     std::map<std::string, void (*)()> suites = {
-        {"msg", t_msg}, {"nodefile", t_nodefile}, {"nodefile_numa", t_nodefile_numa}, {"ring", t_ring}, {"tables", t_tables}, {"tables_mt", t_tables_mt},
+        {"msg", t_msg}, {"nodefile", t_nodefile}, {"nodefile_numa", t_nodefile_numa}, {"ring", t_ring}, {"tables", t_tables}, {"tables_mt", t_tables_mt}, {"slabs", t_slabs},
         {"governor", t_governor}, {"topo", t_topo}, {"pmsg", t_pmsg}, {"sock", t_sock}, {"oracle", t_oracle}};
     int ran = 0;
     for (auto &kv : suites) {
