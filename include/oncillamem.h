@@ -190,8 +190,9 @@ struct ocm_share_token {
     int32_t  rank;
     uint32_t region;
     uint32_t generation;
-    uint32_t tier;        /* 0 pinned host, 1 HBM */
+    uint32_t tier;        /* 0 HBM, 1 pinned host, OCM_SHARE_TIER_MULTICAST: a range of the NVLS region */
 };
+#define OCM_SHARE_TIER_MULTICAST 2u
 /* The far side of a pair or the memory of a local kind; -OCM_EUNSUPPORTED for multi-slab kinds and for
  * local kinds that fell back to malloc / cudaMalloc (src/lib.c:226,240 behaviour). */
 int ocm_share(ocm_alloc_t a, struct ocm_share_token *out);

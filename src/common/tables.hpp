@@ -38,6 +38,10 @@ constexpr uint32_t kTableVersion = 7;
 constexpr uint32_t kMaxGranules  = 1u << 18;
 constexpr uint64_t kMcGranule     = 64ull << 10;
 constexpr uint32_t kMcMaxGranules = 1u << 14;     // multicast region <= 1 GiB
+// The first granules of the multicast region hold one 64-bit completion word per granule of the region (word g
+// belongs to the allocation that STARTS at granule g).  They are part of the region, i.e. bound to the multicast
+// object: a multimem.red on the word's multicast address bumps the word on every GPU at once.
+constexpr uint32_t kMcSignalGranules = (uint32_t)((uint64_t)kMcMaxGranules * 8 / kMcGranule);   // 2
 enum McState : uint32_t { MC_NONE = 0, MC_CREATED = 1, MC_READY = 2, MC_FAILED = 3 };
 
 enum RegionState : uint32_t { REGION_FREE = 0, REGION_LIVE = 1, REGION_DIRTY = 2, REGION_SCRUBBING = 3 };

@@ -279,6 +279,8 @@ int Daemon::init() {
             if (gpu::mc_create(n_ranks_, mc_bytes_, &mc_, &err)) {
                 cluster_->mc_bytes = mc_bytes_;
                 cluster_->mc_n_granules = (uint32_t)(mc_bytes_ / kMcGranule);
+                // the signal words of the region (tables.hpp, kMcSignalGranules) are never handed out
+                cluster_->mc_bitmap[0].fetch_or((1ull << kMcSignalGranules) - 1, std::memory_order_release);
                 cluster_->mc_state.store(MC_CREATED, std::memory_order_release);
                 LOGI("multicast object: %llu bytes over %d devices", (unsigned long long)mc_bytes_, n_ranks_);
             } else {
@@ -1078,9 +1080,11 @@ void Daemon::scrub_loop() {
             mc_dead.clear();
             if (mc_dead_ranges(ct, rank_, &mc_dead)) {
                 char *tail = (char *)gpu_pool_.ptr + tbl_->mc_tail_offset;
-                for (auto &r : mc_dead)
+                for (auto &r : mc_dead) {
                     ocmk::launch_fill(tail + (uint64_t)r.first * kMcGranule, (uint64_t)r.second * kMcGranule, 0,
                                       (cudaStream_t)scrub_stream_);
+                    ocmk::launch_fill(tail + (uint64_t)r.first * 8, 8, 0, (cudaStream_t)scrub_stream_);   // its signal word
+                }
                 cudaStreamSynchronize((cudaStream_t)scrub_stream_);
                 for (auto &r : mc_dead) {
                     scrubbed_bytes_.fetch_add((uint64_t)r.second * kMcGranule, std::memory_order_relaxed);

@@ -90,6 +90,7 @@ cudaError_t launch_put_replicated(void *const *dsts, int n_dst, const void *src,
 // NVLS variant: one multimem.st stream to a multicast VA.
 cudaError_t launch_put_multimem(void *mc_dst, const void *src, size_t bytes, uint64_t *mc_signal, unsigned *ticket,
                                 cudaStream_t stream);
+cudaError_t launch_signal_multimem(uint64_t *mc_signal, cudaStream_t stream);
 // NVLS gather-reduce: dst = element-wise fp32 sum of every GPU's replica behind the multicast VA (multimem.ld_reduce).
 cudaError_t launch_get_reduce_f32(void *dst, const void *mc_src, size_t bytes, cudaStream_t stream);
 

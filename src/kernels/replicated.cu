@@ -98,15 +98,17 @@ __global__ void __launch_bounds__(128, 1) ocm_put_replicated_kernel(RepArgs a) {
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        __threadfence_system();
+        // GPU-scope release on the ticket, one system fence in the CTA that draws the last one (ptx.cuh,
+        // finish_and_signal): cumulativity carries every CTA's stores to the signals that follow
         bool last = true;
         if (gridDim.x > 1) {
-            unsigned t = a.ticket ? atomicAdd(a.ticket, 1u) : 0u;
+            unsigned t = 0;
+            if (a.ticket) asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(t) : "l"(a.ticket) : "memory");
             last = a.ticket && t == gridDim.x - 1;
             if (last) atomicExch(a.ticket, 0u);
         }
         if (last) {
-            __threadfence_system();
+            asm volatile("fence.acq_rel.sys;" ::: "memory");
             for (int d = 0; d < a.n_dst; ++d)
                 if (a.signal[d]) red_release_sys_add(a.signal[d], 1ull);
         }
@@ -124,19 +126,31 @@ __global__ void __launch_bounds__(256) ocm_put_multimem_kernel(uint8_t *mc_dst, 
         multimem_st_v4(mc_dst + i * 16, v);
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence_system();
+    if (threadIdx.x == 0 && mc_signal) {
         bool last = true;
         if (gridDim.x > 1) {
-            unsigned t = ticket ? atomicAdd(ticket, 1u) : 0u;
+            unsigned t = 0;
+            if (ticket) asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(t) : "l"(ticket) : "memory");
             last = ticket && t == gridDim.x - 1;
             if (last) atomicExch(ticket, 0u);
         }
-        if (last && mc_signal) {
-            __threadfence_system();
+        if (last) {
+            // every replica's completion word moves at once: one reduction on the word's multicast address
+            asm volatile("fence.acq_rel.sys;" ::: "memory");
             multimem_red_release_sys_add(mc_signal, 1ull);
         }
     }
+}
+
+// +1 on the completion word of a multicast-backed allocation on every GPU, ordered after prior work on the stream
+// (for puts that could not take the multimem.st path: odd alignment, unaligned tails).
+__global__ void ocm_signal_multimem_kernel(uint64_t *mc_signal) {
+    asm volatile("fence.acq_rel.sys;" ::: "memory");
+    multimem_red_release_sys_add(mc_signal, 1ull);
+}
+cudaError_t launch_signal_multimem(uint64_t *mc_signal, cudaStream_t stream) {
+    ocm_signal_multimem_kernel<<<1, 1, 0, stream>>>(mc_signal);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_put_replicated(void *const *dsts, int n_dst, const void *src, size_t bytes,

@@ -444,19 +444,69 @@ static bool ensure_mc() {
     return true;
 }
 
-// Release a multicast-backed replicated allocation: zero every replica, then give the range back.
+// Point `a` at the range [off, off + per) of the multicast region: one replica per rank, the multicast address of
+// the range, and its completion word (word off / kMcGranule at the start of the region).  False if some rank's
+// slice cannot be mapped from here.
+static bool bind_mc_range(lib_alloc *a, uint64_t off, uint64_t per) {
+    Ctx &c = ctx();
+    const int N = c.n_ranks;
+    a->stripes.assign(N, Side());
+    const uint64_t word = off / kMcGranule * 8;
+    a->mc_sig_near = nullptr;
+    for (int r = 0; r < N; ++r) {
+        RankView *v = get_view(r, true);
+        if (!v || !v->gpu.ptr || v->hdr->mc_bytes < off + per) {
+            for (auto &s : a->stripes) s = Side();
+            return false;
+        }
+        Side &s = a->stripes[r];
+        s.backing = SIDE_MC;
+        s.tier = TIER_GPU;
+        s.rank = r;
+        s.offset = v->hdr->mc_tail_offset + off;
+        s.bytes = per;
+        s.ptr = (char *)v->gpu.ptr + s.offset;
+        // the replica on our own GPU if there is one, else the first
+        if (!a->mc_sig_near || v->hdr->gpu_index == c.device)
+            a->mc_sig_near = reinterpret_cast<uint64_t *>((char *)v->gpu.ptr + v->hdr->mc_tail_offset + word);
+    }
+    a->mc = true;
+    a->mc_offset = off;
+    a->stripe_bytes = per;
+    a->mc_ptr = (char *)c.mc.va + off;
+    a->mc_sig = reinterpret_cast<uint64_t *>((char *)c.mc.va + word);
+    return true;
+}
+
+// Completion word of a multicast-backed allocation, read from the nearest replica (HBM: a small device-to-host copy).
+static int mc_signal_value(lib_alloc *a, uint64_t *out) {
+    Ctx &c = ctx();
+    if (!a->mc_sig_near || c.device < 0) return OCM_EUNSUPPORTED;
+    DeviceGuard dg(c.device);
+    return cudaMemcpy(out, a->mc_sig_near, 8, cudaMemcpyDeviceToHost) == cudaSuccess ? OCM_OK : OCM_ECUDA;
+}
+
+// Release a multicast-backed replicated allocation: zero every replica and its completion word, then give the
+// range back.  A handle opened with ocm_attach only lets go.
 static void release_mc(lib_alloc *a) {
     Ctx &c = ctx();
-    if (c.device >= 0 && c.stream) {
-        DeviceGuard dg(c.device);
-        for (auto &s : a->stripes)
-            if (s.ptr) ocmk::launch_fill(s.ptr, a->stripe_bytes, 0, (cudaStream_t)c.stream);
-        cudaStreamSynchronize((cudaStream_t)c.stream);
+    if (!a->mc_attached) {
+        if (c.device >= 0 && c.stream) {
+            DeviceGuard dg(c.device);
+            const uint64_t word = a->mc_offset / kMcGranule * 8;
+            for (auto &s : a->stripes) {
+                if (!s.ptr) continue;
+                ocmk::launch_fill(s.ptr, a->stripe_bytes, 0, (cudaStream_t)c.stream);
+                ocmk::launch_fill((char *)s.ptr - a->mc_offset + word, 8, 0, (cudaStream_t)c.stream);
+            }
+            cudaStreamSynchronize((cudaStream_t)c.stream);
+        }
+        mc_range_free(c.cluster, a->mc_offset, a->stripe_bytes);
+        c.bytes_live[TIER_GPU].fetch_sub(a->stripe_bytes, std::memory_order_relaxed);
     }
-    mc_range_free(c.cluster, a->mc_offset, a->stripe_bytes);
-    c.bytes_live[TIER_GPU].fetch_sub(a->stripe_bytes, std::memory_order_relaxed);
     for (auto &s : a->stripes) s = Side();
     a->mc = false;
+    a->mc_sig = a->mc_sig_near = nullptr;
 }
 
 static bool valid_handle(ocm_alloc_t a) { return a && a->magic == kAllocMagic; }
@@ -697,27 +747,11 @@ ocm_alloc_t ocm_alloc_ex(const struct ocm_alloc_params_ex *p) {
         // replicated: prefer the NVLS multicast region (one range, same offset on every GPU)
         if (kind == OCM_REPLICATED_GPU && ensure_mc()) {
             int64_t off = mc_range_alloc(c.cluster, per, (int)getpid(), c.rank);   // owner-tracked: reclaimed if we die
-            bool ok = off >= 0;
-            for (int r = 0; r < N && ok; ++r) {
-                RankView *v = get_view(r, true);
-                ok = v && v->gpu.ptr && v->hdr->mc_bytes >= (uint64_t)off + per;
-                if (!ok) break;
-                Side &s = a->stripes[r];
-                s.backing = SIDE_MC;
-                s.tier = TIER_GPU;
-                s.rank = r;
-                s.offset = v->hdr->mc_tail_offset + (uint64_t)off;
-                s.bytes = per;
-                s.ptr = (char *)v->gpu.ptr + s.offset;
-            }
-            if (ok) {
-                a->mc = true;
-                a->mc_offset = (uint64_t)off;
-                a->mc_ptr = (char *)c.mc.va + off;
+            if (off >= 0 && bind_mc_range(a, (uint64_t)off, per)) {
                 c.bytes_live[TIER_GPU].fetch_add(per, std::memory_order_relaxed);
             } else {
                 if (off >= 0) mc_range_free(c.cluster, (uint64_t)off, per);
-                for (auto &s : a->stripes) s = Side();
+                a->stripes.assign(N, Side());
             }
         }
         for (int r = 0; r < N && !err && !a->mc; ++r)
@@ -844,6 +878,7 @@ int ocm_is_multicast(ocm_alloc_t a) { return valid_handle(a) && a->mc ? 1 : 0; }
 
 int ocm_signal_read(ocm_alloc_t a, uint64_t *value) {
     if (!valid_handle(a) || !value) return -OCM_EINVAL;
+    if (a->mc) return -mc_signal_value(a, value);
     const Side &s = (a->paired && a->remote.valid()) ? a->remote : a->local;
     if (!s.rec) return -OCM_EUNSUPPORTED;
     *value = region_signal_total(s.hdr, *s.rec);
@@ -853,9 +888,16 @@ int ocm_signal_read(ocm_alloc_t a, uint64_t *value) {
 int ocm_signal_wait(ocm_alloc_t a, uint64_t at_least, int timeout_ms) {
     if (!valid_handle(a)) return -OCM_EINVAL;
     const Side &s = (a->paired && a->remote.valid()) ? a->remote : a->local;
-    if (!s.rec) return -OCM_EUNSUPPORTED;
+    if (!s.rec && !a->mc) return -OCM_EUNSUPPORTED;
     uint64_t deadline = mono_ns() + (uint64_t)(timeout_ms < 0 ? 0 : timeout_ms) * 1000000ull;
     for (unsigned spin = 0;; ++spin) {
+        if (a->mc) {   // the word lives in HBM: every look is a small device-to-host copy
+            uint64_t v = 0;
+            if (int e = mc_signal_value(a, &v)) return -e;
+            if (v >= at_least) return 0;
+            if (timeout_ms >= 0 && mono_ns() > deadline) return -OCM_ESTALE;
+            continue;
+        }
         if (region_signal_total(s.hdr, *s.rec) >= at_least) return 0;
         if (timeout_ms >= 0 && mono_ns() > deadline) return -OCM_ESTALE;
         if (spin > 1000) usleep(20);
@@ -885,6 +927,18 @@ static int gpu_slot() {
 
 int ocm_share(ocm_alloc_t a, struct ocm_share_token *out) {
     if (!valid_handle(a) || !out) return -OCM_EINVAL;
+    if (a->mc && ctx().cluster) {
+        // a multicast-backed allocation is named by its range of the region; the owner word in the cluster table
+        // (pid, length, rank) is what an attaching application checks it against
+        const uint32_t g = (uint32_t)(a->mc_offset / kMcGranule);
+        memset(out, 0, sizeof *out);
+        out->id = ctx().cluster->mc_owner[g].load(std::memory_order_acquire);
+        out->bytes = a->stripe_bytes;
+        out->rank = mc_owner_rank(out->id);
+        out->region = g;
+        out->tier = OCM_SHARE_TIER_MULTICAST;
+        return mc_owner_state(out->id) == MC_RANGE_OWNED ? 0 : -OCM_ESTALE;
+    }
     const Side *s = shareable_side(a);
     if (!s) return -OCM_EUNSUPPORTED;
     // a shared block gets per-writer completion counters (tables.hpp, SigExt) before anybody can attach
@@ -905,6 +959,35 @@ int ocm_attach(const struct ocm_share_token *tok, ocm_alloc_t *out) {
     if (!tok || !out) return -OCM_EINVAL;
     *out = nullptr;
     if (!c.inited || !c.cluster) return -OCM_ENODAEMON;
+    if (tok->tier == OCM_SHARE_TIER_MULTICAST) {
+        // the same range of the NVLS region, opened by another application: puts through this handle reach every
+        // replica and bump the same completion word; freeing it only lets go
+        if (c.device < 0) return -OCM_ENOGPU;
+        if (!ensure_mc()) return -OCM_EUNSUPPORTED;
+        if (tok->region < kMcSignalGranules || tok->region >= c.cluster->mc_n_granules) return -OCM_EINVAL;
+        const uint64_t w = c.cluster->mc_owner[tok->region].load(std::memory_order_acquire);
+        if (w != tok->id || mc_owner_state(w) != MC_RANGE_OWNED ||
+            (uint64_t)mc_owner_granules(w) * kMcGranule < tok->bytes)
+            return -OCM_ESTALE;
+        lib_alloc *a = new lib_alloc();
+        a->magic = kAllocMagic;
+        a->kind = OCM_REPLICATED_GPU;
+        a->paired = true;
+        a->lib_stream_pending.store(false);
+        a->mc_attached = true;
+        if (!bind_mc_range(a, (uint64_t)tok->region * kMcGranule, tok->bytes)) {
+            a->magic = 0;
+            delete a;
+            return -OCM_ENOGPU;
+        }
+        {
+            std::lock_guard<std::mutex> g(c.mu);
+            c.allocs.insert(a);
+        }
+        c.n_alloc.fetch_add(1, std::memory_order_relaxed);
+        *out = a;
+        return 0;
+    }
     if (tok->rank < 0 || tok->rank >= c.n_ranks || tok->tier >= (uint32_t)TIER_COUNT) return -OCM_EINVAL;
     if (tok->tier == TIER_GPU && c.device < 0) return -OCM_ENOGPU;
     RankView *v = get_view(tok->rank, tok->tier == TIER_GPU);

@@ -343,8 +343,9 @@ static int stripes_xfer(ocm_alloc_t a, bool to_far, const Side &local, uint64_t 
         if (a->mc && aligned && n % 16 == 0 && local.tier == TIER_GPU && c.device >= 0) {
             // NVLS: one multimem.st stream, the switch replicates it into every GPU's slice
             DeviceGuard dg(c.device);
+            // ... and the allocation's completion word on every GPU (multimem.red on the word's multicast address)
             cudaError_t e = ocmk::launch_put_multimem((char *)a->mc_ptr + far_off, (const char *)local.ptr + local_off, n,
-                                                      nullptr, next_ticket(), (cudaStream_t)(stream ? stream : c.stream));
+                                                      a->mc_sig, next_ticket(), (cudaStream_t)(stream ? stream : c.stream));
             ++c.kernel_launches;
             note_other_gpu_op();
             c.n_copies.fetch_add(1, std::memory_order_relaxed);
@@ -367,11 +368,24 @@ static int stripes_xfer(ocm_alloc_t a, bool to_far, const Side &local, uint64_t 
             c.n_copies.fetch_add(1, std::memory_order_relaxed);
             c.copy_bytes.fetch_add(n * N, std::memory_order_relaxed);
             *used = true;
+            if (e == cudaSuccess && a->mc && a->mc_sig) {
+                e = ocmk::launch_signal_multimem(a->mc_sig, (cudaStream_t)(stream ? stream : c.stream));
+                ++c.kernel_launches;
+            }
             return cuda_err(e, "replicated put");
         }
         for (size_t r = 0; r < N; ++r) {
             int err = side_copy(a->stripes[r], far_off, nullptr, 0, local, local_off, n, &a->stripes[r], stream, used);
             if (err) return err;
+        }
+        if (a->mc && a->mc_sig && c.device >= 0) {
+            // per-replica copies of a multicast-backed allocation: its completion word still moves once, everywhere
+            DeviceGuard dg(c.device);
+            cudaError_t e = ocmk::launch_signal_multimem(a->mc_sig, (cudaStream_t)(stream ? stream : c.stream));
+            ++c.kernel_launches;
+            note_other_gpu_op();
+            *used = true;
+            return cuda_err(e, "multicast signal");
         }
         return OCM_OK;
     }

@@ -103,6 +103,11 @@ struct lib_alloc {
     bool          mc;                 // replicated through the NVLS multicast region
     uint64_t      mc_offset;          // offset of this allocation inside the region
     void         *mc_ptr;             // its multicast virtual address
+    // completion word of a multicast-backed allocation (tables.hpp, kMcSignalGranules): its multicast address (a
+    // multimem.red there bumps the word on every GPU) and the copy of it in the replica nearest to this process
+    uint64_t     *mc_sig = nullptr;
+    uint64_t     *mc_sig_near = nullptr;
+    bool          mc_attached = false;   // opened with ocm_attach: the range belongs to another application
     std::atomic<bool> lib_stream_pending;
 };
 

@@ -263,6 +263,68 @@ def test_nvls_multicast_replicated_put(gpu_cluster):
     b.free()
 
 
+NVLS_WAITER = r"""
+import sys, torch, oncilla_b200 as ocm
+from oncilla_b200 import ops
+ocm.init()
+b = ocm.attach(bytes.fromhex(sys.argv[1]))
+assert b.is_multicast and b.kind == ocm.OCM_REPLICATED_GPU
+n = int(sys.argv[2])
+print("WAITING", flush=True)
+b.wait_signal(1, timeout_ms=20000)                      # rank 0's multicast put bumps OUR replica's word too
+mine = b.slab_tensor(ocm.rank())
+bad = ops.verify(mine[:n], 0xFEEDFACE12345678, n)
+# and the other way: this application puts into the same range from its own GPU
+src = ocm.alloc(ocm.OCM_LOCAL_GPU, n)
+ops.fill(src.local_tensor(), 0x0BADF00D0BADF00D)
+torch.cuda.synchronize()
+ocm.copy(b, src, n)
+sig = b.signal()
+b.free(); src.free()
+ocm.tini()
+print("RESULT", bad, sig)
+"""
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="NVLS multicast needs two GPUs")
+def test_nvls_completion_signal_reaches_every_replica(gpu_cluster):
+    """A multimem.st put ends with multimem.red on the allocation's completion word: an application on rank 1 that
+    attached to the same range sees rank 0's put on ITS replica (ocm_signal_wait), and its own put counts here."""
+    import subprocess
+    import sys
+    import time
+
+    from conftest import REPO
+    from oncilla_b200 import api
+
+    if not api.multicast_ready(wait_s=10.0):
+        pytest.skip("NVLS multicast not available on this box")
+    n = 1 << 20
+    a = ocm.alloc(ocm.OCM_REPLICATED_GPU, n, n)
+    assert a.is_multicast and a.signal() == 0
+    env = gpu_cluster.env(1)
+    env["PYTHONPATH"] = str(REPO)
+    p = subprocess.Popen([sys.executable, "-c", NVLS_WAITER, a.share().hex(), str(n)], env=env, stdout=subprocess.PIPE,
+                         stderr=subprocess.PIPE, text=True)
+    assert "WAITING" in p.stdout.readline()
+    time.sleep(0.3)
+    ops.fill(a.local_tensor(), 0xFEEDFACE12345678)
+    torch.cuda.synchronize()
+    a.put(n)
+    assert a.signal() == 1
+    out, err = p.communicate(timeout=120)
+    assert p.returncode == 0 and "RESULT 0 2" in out, out[-1000:] + err[-2000:]
+    a.wait_signal(2, timeout_ms=5000)
+    assert ops.verify(a.slab_tensor(0)[:n], 0x0BADF00D0BADF00D, n) == 0      # rank 1's put landed in our replica
+    # an unaligned put takes per-replica stores, and still counts once on every replica
+    a.put(1000, src_offset=3, dest_offset=77)
+    assert a.signal() == 3
+    a.free()
+    c = ocm.alloc(ocm.OCM_REPLICATED_GPU, n, n)                              # same range again: word back at zero
+    assert c.is_multicast and c.signal() == 0
+    c.free()
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="NVLS multicast needs two GPUs")
 def test_nvls_gather_reduce(gpu_cluster):
     """multimem.ld_reduce: the window receives the fp32 sum of every rank's replica, added inside the NVSwitch."""
@@ -332,7 +394,8 @@ def test_nvls_range_of_dead_application_is_reclaimed(gpu_cluster):
     N = ocm.num_ranks()
     r = run_py(gpu_cluster, N - 1, MC_LEAK)
     assert r.returncode == 0 and "LEAKED" in r.stdout, r.stdout + r.stderr
-    region = 256 << 20                                      # OCM_MC_BYTES default: only a fully free region fits this
+    # OCM_MC_BYTES default minus the granules that hold the region's completion words: only a fully free region fits
+    region = (256 << 20) - (128 << 10)
     a, t0 = None, time.time()
     while time.time() - t0 < 15:
         a = ocm.alloc(ocm.OCM_REPLICATED_GPU, 4096, region)
