@@ -66,3 +66,15 @@ def run_py(cl, rank, code, timeout=180, env_extra=None, argv=()):
     if env_extra:
         env.update(env_extra)
     return subprocess.run([sys.executable, "-c", code, *argv], env=env, capture_output=True, text=True, timeout=timeout)
+
+
+def pytest_terminal_summary(terminalreporter, exitstatus, config):
+    """One line that names every skipped test: a GPU lease with fewer devices than a test needs must show up in the
+    log as a visible gap, not as a silent 's'."""
+    skipped = terminalreporter.stats.get("skipped", [])
+    if not skipped:
+        return
+    names = sorted({r.nodeid.split("::", 1)[-1] for r in skipped})
+    why = sorted({str(r.longrepr[-1]) if isinstance(r.longrepr, tuple) else str(r.longrepr) for r in skipped})
+    terminalreporter.write_line(f"SKIPPED ({len(names)}): " + ", ".join(names))
+    terminalreporter.write_line("SKIP REASONS: " + " | ".join(w[:120] for w in why))

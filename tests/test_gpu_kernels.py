@@ -4,6 +4,8 @@ References: the C++ oracles in src/oracle (through the C ABI) and plain PyTorch 
 The reference project has no kernels to compare with; its copy semantics are memcpy with
 the same offsets (reference src/lib.c:523), which is what the copy tests assert.
 """
+import ctypes
+
 import pytest
 import torch
 
@@ -273,12 +275,20 @@ def test_sort_u64_matches_oracle(n):
     next pass's histogram) and of the one-tile-per-CTA boundary."""
     g = torch.Generator(device="cuda")
     g.manual_seed(n)
-    keys = torch.randint(0, 2**62, (n,), dtype=torch.int64, device="cuda", generator=g)
+    # the full 64-bit range: about half of the keys have bit 63 set (negative as int64, LARGEST as unsigned keys)
+    keys = torch.randint(-2**63, 2**63 - 1, (n,), dtype=torch.int64, device="cuda", generator=g)
     keys[: n // 3] = keys[: n // 3] & 0xFFFF        # plenty of duplicates and small keys
-    want = torch.sort(keys).values
+    keys[n // 2:n // 2 + 3] = torch.tensor([-1, -2**63, 2**63 - 1], dtype=torch.int64, device="cuda")[: max(0, min(3, n - n // 2))]
+    # unsigned order = signed order after flipping the sign bit
+    flip = torch.tensor(-2**63, dtype=torch.int64, device="cuda")
+    want = torch.sort(keys ^ flip).values ^ flip
+    host = keys.cpu().clone()
     ops.sort_u64(keys)
     torch.cuda.synchronize()
     assert torch.equal(keys, want)
+    if n <= 100_003:                                 # and against the plain C++ oracle (std::sort on uint64_t)
+        ocm._native.lib.ocm_oracle_sort_u64(ctypes.c_void_p(host.data_ptr()), host.numel())
+        assert torch.equal(keys.cpu(), host)
 
 
 def test_launch_counter_counts_our_kernels():

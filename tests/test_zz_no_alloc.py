@@ -25,9 +25,15 @@ lib = ocm._native.lib
 def _keys(n, seed):
     g = torch.Generator(device="cuda")
     g.manual_seed(seed)
-    k = torch.randint(0, 2**62, (n,), dtype=torch.int64, device="cuda", generator=g)
+    # full 64-bit range: keys with bit 63 set are negative as int64 but the LARGEST as unsigned sort keys
+    k = torch.randint(-2**63, 2**63 - 1, (n,), dtype=torch.int64, device="cuda", generator=g)
     k[: n // 4] &= 0xFFFFF          # duplicates and short keys exercise every digit position
     return k
+
+
+def _unsigned_sorted(keys):
+    flip = torch.tensor(-2**63, dtype=torch.int64, device=keys.device)
+    return torch.sort(keys ^ flip).values ^ flip
 
 
 def _sort(fn, keys):
@@ -46,7 +52,28 @@ def test_noalloc_sort_matches_regular_entry_point_twice():
         rc_new, got = _sort(lib.ocmk_sort_u64_noalloc, keys)
         assert rc_ref == 0 and rc_new == 0, (call, rc_ref, rc_new)
         assert torch.equal(got, want), f"call {call}: outputs differ"        # exact: same tolerance as the sort tests
-        assert torch.equal(got, torch.sort(keys).values)
+        assert torch.equal(got, _unsigned_sorted(keys))
+        host = keys.cpu().clone()                                             # and the plain C++ oracle
+        lib.ocm_oracle_sort_u64(ctypes.c_void_p(host.data_ptr()), host.numel())
+        assert torch.equal(got.cpu(), host)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs a second GPU")
+def test_noalloc_sort_on_a_second_device():
+    """The scratch array exists once per GPU and its address is looked up per device: a call on GPU 1 (first use
+    there) must not reuse GPU 0's address."""
+    torch.cuda.set_device(0)
+    _sort(lib.ocmk_sort_u64_noalloc, _keys(50_000, 5))                        # make sure GPU 0's address is cached first
+    try:
+        torch.cuda.set_device(1)
+        keys = _keys(200_000, 9).to("cuda:1")
+        work, tmp = keys.clone(), torch.empty_like(keys)
+        rc = lib.ocmk_sort_u64_noalloc(ctypes.c_void_p(work.data_ptr()), ctypes.c_void_p(tmp.data_ptr()), keys.numel(),
+                                       ctypes.c_void_p(int(torch.cuda.current_stream().cuda_stream)))
+        torch.cuda.synchronize()
+        assert rc == 0 and torch.equal(work, _unsigned_sorted(keys))
+    finally:
+        torch.cuda.set_device(0)
 
 
 def test_noalloc_sort_rejects_oversize_without_launching():
