@@ -61,10 +61,24 @@ def main():
             tc.barrier()
             worst = allmax(g["seconds"], world)
             ok = allsum(1.0 if g["verified"] else 0.0, world) == world
+            tc.barrier()
+            gl = gups.run(total_words=args.gups_words, n_updates=args.gups_updates, iters=3, local_only=True)
+            tc.barrier()
+            worst_local = allmax(gl["seconds"], world)
         if rank == 0 and not args.only:
+            # Roofline of the pooled case: an 8-byte RED is one NVLink request of at least 32 bytes on the wire
+            # (16-byte header + payload flit), so 900 GB/s per direction carries at most ~28 G remote updates/s per GPU;
+            # (world-1)/world of the updates are remote.
+            per_gpu = args.gups_updates / worst / 1e9
+            remote_frac = (world - 1) / world if world > 1 else 0.0
             print(json.dumps({"kind": "gups", "n_gpus": world, "table_words_per_rank": args.gups_words,
                               "updates_per_rank": args.gups_updates, "seconds_max": round(worst, 6),
-                              "GUPS_aggregate": round(world * args.gups_updates / worst / 1e9, 3), "verified": ok}), flush=True)
+                              "GUPS_aggregate": round(world * args.gups_updates / worst / 1e9, 3),
+                              "GUPS_per_gpu": round(per_gpu, 3),
+                              "GUPS_per_gpu_local_hbm_only": round(args.gups_updates / worst_local / 1e9, 3),
+                              "nvlink_packet_bound_GUPS_per_gpu": round(900.0 / 32.0 / remote_frac, 1) if remote_frac else None,
+                              "frac_of_nvlink_packet_bound": round(per_gpu * remote_frac / (900.0 / 32.0), 3) if remote_frac else None,
+                              "verified": ok and bool(gl["verified"])}), flush=True)
         # ---- config 4 ------------------------------------------------------------------------
         tc.barrier()
         # half of the runs (and of the output) fit the HBM budget, the rest spills to the pinned host tier

@@ -12,12 +12,13 @@ from ..parallel import StripedTable
 
 
 def run(total_words: int = 1 << 26, n_updates: int = 1 << 26, words_per_stripe: int = 1 << 16, seed: int = 7,
-        iters: int = 3, verify: bool = True) -> dict:
+        iters: int = 3, verify: bool = True, local_only: bool = False) -> dict:
     import torch
 
     from .. import api
 
-    tab = StripedTable(total_words, words_per_stripe)
+    # local_only: the whole table in this rank's own HBM (no NVLink) - the reference point for the pooled number
+    tab = StripedTable(total_words, words_per_stripe, ranks=[api.rank()] if local_only else None)
     try:
         # far sides start zeroed; keep it that way (xor stream applied twice must give zeros back)
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -35,17 +35,20 @@ class StripedTable:
     into the calling process, so device code addresses any word directly (K7 GUPS).
     """
 
-    def __init__(self, total_words: int, words_per_stripe: int = 1 << 16, n_ranks: int | None = None):
+    def __init__(self, total_words: int, words_per_stripe: int = 1 << 16, n_ranks: int | None = None,
+                 ranks: list[int] | None = None):
         from .. import api
 
         assert total_words & (total_words - 1) == 0 and words_per_stripe & (words_per_stripe - 1) == 0
-        self.n_ranks = n_ranks or api.num_ranks()
+        # ranks: the ranks that hold slab 0, 1, ... (default: all of them in order; [api.rank()] = one local HBM)
+        self.ranks = list(ranks) if ranks is not None else list(range(n_ranks or api.num_ranks()))
+        self.n_ranks = len(self.ranks)
         self.total_words = total_words
         self.words_per_stripe = min(words_per_stripe, total_words)
         stripes = total_words // self.words_per_stripe
         per_rank_stripes = (stripes + self.n_ranks - 1) // self.n_ranks
         self.slab_bytes = per_rank_stripes * self.words_per_stripe * 8
-        self.slabs = [alloc_on(r, self.slab_bytes) for r in range(self.n_ranks)]
+        self.slabs = [alloc_on(r, self.slab_bytes) for r in self.ranks]
 
     @property
     def bases(self) -> list[int]:

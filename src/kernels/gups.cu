@@ -10,7 +10,10 @@
 
 namespace ocmk {
 
-constexpr uint64_t kGupsThreads = 1ull << 17;
+// Grid: four CTAs of 256 threads per SM.  The update stream is a function of (thread, step) with the thread count
+// as a parameter, so the CPU oracle (ocm_oracle_gups) is told the same count (gups_threads()).
+constexpr int kGupsCtasPerSm = 4;
+uint64_t gups_threads() { return (uint64_t)num_sms() * kGupsCtasPerSm * 256; }
 
 __device__ __forceinline__ uint64_t mix64(uint64_t z) {
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -30,10 +33,23 @@ __device__ __forceinline__ uint64_t *gups_addr(const GupsTable &t, uint64_t idx,
 
 __global__ void __launch_bounds__(256) ocm_gups_kernel(GupsTable t, uint64_t n_updates, uint64_t seed, unsigned shift) {
     const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t T = (uint64_t)gridDim.x * blockDim.x;
     const uint64_t mask = t.total_words - 1;
     uint64_t step = 0;
-    // 4 independent updates in flight per thread
-    for (uint64_t u = tid; u < n_updates; u += kGupsThreads, ++step) {
+    // four updates per iteration: all four values and addresses are computed before the first reduction is issued,
+    // so the hashing of update k+1..k+3 overlaps the issue of update k (a RED returns nothing: nothing waits on it)
+    uint64_t u = tid;
+    for (; u + 3 * T < n_updates; u += 4 * T, step += 4) {
+        uint64_t v[4], *p[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            v[k] = mix64(seed + tid * 0x9E3779B97F4A7C15ull + (step + k) * 0xD1B54A32D192ED03ull);
+            p[k] = gups_addr(t, v[k] & mask, shift);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) asm volatile("red.global.xor.b64 [%0], %1;" ::"l"(p[k]), "l"(v[k]) : "memory");
+    }
+    for (; u < n_updates; u += T, ++step) {
         uint64_t v = mix64(seed + tid * 0x9E3779B97F4A7C15ull + step * 0xD1B54A32D192ED03ull);
         uint64_t *p = gups_addr(t, v & mask, shift);
         asm volatile("red.global.xor.b64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -58,7 +74,7 @@ cudaError_t launch_gups(const GupsTable &t, uint64_t n_updates, uint64_t seed, c
         return cudaErrorInvalidValue;
     if (t.total_words / t.words_per_stripe > 0xFFFFFFFFull) return cudaErrorInvalidValue;
     const unsigned shift = (unsigned)__builtin_ctzll(t.words_per_stripe);
-    ocm_gups_kernel<<<(unsigned)(kGupsThreads / 256), 256, 0, stream>>>(t, n_updates, seed, shift);
+    ocm_gups_kernel<<<(unsigned)(gups_threads() / 256), 256, 0, stream>>>(t, n_updates, seed, shift);
     return cudaGetLastError();
 }
 

@@ -102,6 +102,7 @@ struct GupsTable {
     uint64_t  total_words;        // power of two
 };
 cudaError_t launch_gups(const GupsTable &t, uint64_t n_updates, uint64_t seed, cudaStream_t stream);
+uint64_t gups_threads();   // threads launch_gups uses on the current device (the oracle needs the same number)
 cudaError_t launch_gups_init(const GupsTable &t, int my_rank, cudaStream_t stream);
 
 // ---- K8: radix sort of u64 keys -------------------------------------------------------

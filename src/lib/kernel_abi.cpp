@@ -136,7 +136,7 @@ int ocmk_gups(uint64_t *const *bases, int n_ranks, uint64_t words_per_stripe, ui
     ++g_abi_launches;
     return ret(ocmk::launch_gups(t, n_updates, seed, (cudaStream_t)stream), "ocmk_gups");
 }
-uint64_t ocmk_gups_threads(uint64_t) { return 1ull << 17; }
+uint64_t ocmk_gups_threads(uint64_t) { return ocmk::gups_threads(); }
 
 int ocmk_sort_u64(uint64_t *keys, uint64_t *tmp, uint64_t n, void *stream) {
     int dev = 0;
