@@ -74,6 +74,12 @@ int ocmk_sort_u64(uint64_t *keys, uint64_t *tmp, uint64_t n, void *stream);
 #define OCMK_SORT_NOALLOC_MAX_KEYS (1ull << 24)
 int ocmk_sort_u64_noalloc(uint64_t *keys, uint64_t *tmp, uint64_t n, void *stream);
 
+/* K8 merge: out = stable merge of two ascending unsigned 64-bit sequences (merge-path tiles).  ocmk_merge_runs_u64
+ * merges k runs laid end to end (run i = keys[offsets[i] .. offsets[i+1]), offsets on the host) by ceil(log2 k)
+ * levels of pairwise merges between keys and tmp; it returns 0 if the result ends in keys, 1 if in tmp. */
+int ocmk_merge_u64(const uint64_t *a, uint64_t na, const uint64_t *b, uint64_t nb, uint64_t *out, void *stream);
+int ocmk_merge_runs_u64(uint64_t *keys, uint64_t *tmp, const uint64_t *offsets, int k, void *stream);
+
 /* number of kernels launched through this ABI and the ocm_* calls so far */
 uint64_t ocmk_launch_count(void);
 

@@ -183,6 +183,8 @@ _sig("ocm_oracle_checksum", C.c_uint64, C.c_void_p, C.c_size_t)
 _sig("ocm_oracle_strided_copy", C.c_int, P(ocmk_strided))
 _sig("ocm_oracle_gups", None, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64)
 _sig("ocm_oracle_sort_u64", None, C.c_void_p, C.c_size_t)
+_sig("ocmk_merge_u64", C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p)
+_sig("ocmk_merge_runs_u64", C.c_int, C.c_void_p, C.c_void_p, P(C.c_uint64), C.c_int, C.c_void_p)
 _sig("ocm_oracle_f32_to_e4m3", C.c_uint8, C.c_float)
 _sig("ocm_oracle_e4m3_to_f32", C.c_float, C.c_uint8)
 

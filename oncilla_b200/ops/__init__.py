@@ -133,6 +133,15 @@ def sort_u64(keys, tmp=None, *, stream=None) -> None:
            "ocmk_sort_u64")
 
 
+def merge_runs(keys, tmp, offsets, *, stream=None):
+    """K8 merge: ``keys`` holds ``len(offsets) - 1`` ascending runs laid end to end (run i = keys[offsets[i]:offsets[i+1]]);
+    returns the tensor (``keys`` or ``tmp``) that holds the merged sequence.  Unsigned order, stable."""
+    offs = (C.c_uint64 * len(offsets))(*[int(o) for o in offsets])
+    r = lib.ocmk_merge_runs_u64(C.c_void_p(_ptr(keys)), C.c_void_p(_ptr(tmp)), offs, len(offsets) - 1, _stream(stream))
+    _check(min(r, 0), "ocmk_merge_runs_u64")
+    return tmp if r == 1 else keys
+
+
 def launch_count() -> int:
     return int(lib.ocmk_launch_count())
 

@@ -136,6 +136,16 @@ struct ServerCtl {
 cudaError_t launch_copy_server(ServerDesc *ring, uint32_t ring_size, ServerCtl *ctl, uint64_t start_seq, uint64_t idle_ns,
                                uint64_t max_ns, cudaStream_t stream);
 
+// ---- K8: merge of sorted u64 runs -----------------------------------------------------------------------
+// out = stable merge of a[0..na) and b[0..nb) (both ascending, unsigned).  One launch handles many pairs.
+struct MergePairDesc {
+    const uint64_t *a, *b;
+    uint64_t       *out;
+    uint64_t        na, nb;
+};
+cudaError_t launch_merge_pairs(const MergePairDesc *pairs, int n_pairs, cudaStream_t stream,
+                               unsigned long long *launches = nullptr);
+
 int num_sms(int device = -1);
 // Launches made by entry points that live inside the kernel library (ocmk_sort_u64_noalloc, the copy server);
 // ocmk_launch_count() adds it to the library's own counters.

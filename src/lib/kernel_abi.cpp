@@ -171,6 +171,52 @@ int ocmk_sort_u64(uint64_t *keys, uint64_t *tmp, uint64_t n, void *stream) {
     return ret(e, "ocmk_sort_u64");
 }
 
+int ocmk_merge_u64(const uint64_t *a, uint64_t na, const uint64_t *b, uint64_t nb, uint64_t *out, void *stream) {
+    ocmk::MergePairDesc d{a, b, out, na, nb};
+    unsigned long long nl = 0;
+    cudaError_t e = ocmk::launch_merge_pairs(&d, 1, (cudaStream_t)stream, &nl);
+    g_abi_launches += nl;
+    return ret(e, "ocmk_merge_u64");
+}
+
+// k sorted runs laid end to end in `keys` (run i = keys[offsets[i] .. offsets[i+1])) become one sorted sequence
+// through ceil(log2 k) levels of pairwise merges between `keys` and `tmp`; every level is one launch per 32 pairs.
+// Returns 0 if the result is in `keys`, 1 if it is in `tmp`, or a negative ocm_err.
+int ocmk_merge_runs_u64(uint64_t *keys, uint64_t *tmp, const uint64_t *offsets, int k, void *stream) {
+    if (k < 1 || !keys || !tmp || !offsets) return -OCM_EINVAL;
+    std::vector<uint64_t> off(offsets, offsets + k + 1);
+    for (int i = 0; i < k; ++i)
+        if (off[i] > off[i + 1]) return -OCM_EINVAL;
+    uint64_t *src = keys, *dst = tmp;
+    int where = 0;
+    unsigned long long nl = 0;
+    while (off.size() > 2) {
+        const int runs = (int)off.size() - 1;
+        std::vector<ocmk::MergePairDesc> pairs;
+        std::vector<uint64_t> next{off[0]};
+        for (int i = 0; i < runs; i += 2) {
+            ocmk::MergePairDesc d;
+            d.a = src + off[i];
+            d.na = off[i + 1] - off[i];
+            d.b = i + 1 < runs ? src + off[i + 1] : nullptr;
+            d.nb = i + 1 < runs ? off[i + 2] - off[i + 1] : 0;      // an odd run out is merged with nothing: a copy
+            d.out = dst + off[i];
+            pairs.push_back(d);
+            next.push_back(off[std::min(i + 2, runs)]);
+        }
+        cudaError_t e = ocmk::launch_merge_pairs(pairs.data(), (int)pairs.size(), (cudaStream_t)stream, &nl);
+        if (e != cudaSuccess) {
+            g_abi_launches += nl;
+            return ret(e, "ocmk_merge_runs_u64");
+        }
+        off.swap(next);
+        std::swap(src, dst);
+        where ^= 1;
+    }
+    g_abi_launches += nl;
+    return where;
+}
+
 // ---- strided copies on allocations -------------------------------------------------
 static int strided_sides(const Side &dst, const Side &src, const struct ocm_strided *d, const Side *sig, void *stream) {
     Ctx &c = ctx();

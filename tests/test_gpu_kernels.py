@@ -291,6 +291,28 @@ def test_sort_u64_matches_oracle(n):
         assert torch.equal(keys.cpu(), host)
 
 
+@pytest.mark.parametrize("k,total", [(1, 1000), (2, 5), (2, 100_000), (3, 4096), (7, 300_001), (16, 1 << 20), (33, 2_000_003)])
+def test_merge_runs_matches_sorted_concatenation(k, total):
+    """k sorted runs of uneven length (an empty one among them) merge into the sorted whole; full-range unsigned keys
+    with duplicates, tile edges (2048 outputs per tile) on both sides."""
+    g = torch.Generator(device="cuda")
+    g.manual_seed(k * 1000 + total % 997)
+    flip = torch.tensor(-2**63, dtype=torch.int64, device="cuda")
+    cuts = sorted(int(x) for x in torch.randint(0, total + 1, (k - 1,), generator=torch.Generator().manual_seed(k)))
+    if k > 2:
+        cuts[1] = cuts[0]                                   # an empty run
+    offs = [0] + cuts + [total]
+    keys = torch.randint(-2**63, 2**63 - 1, (total,), dtype=torch.int64, device="cuda", generator=g)
+    keys[: total // 5] &= 0xFF                             # many equal keys across runs
+    keys = keys[torch.randperm(total, device="cuda", generator=g)]
+    for lo, hi in zip(offs[:-1], offs[1:]):
+        keys[lo:hi] = torch.sort(keys[lo:hi] ^ flip).values ^ flip
+    want = torch.sort(keys ^ flip).values ^ flip
+    out = ops.merge_runs(keys, torch.empty_like(keys), offs)
+    torch.cuda.synchronize()
+    assert torch.equal(out, want)
+
+
 def test_launch_counter_counts_our_kernels():
     before = ops.launch_count()
     a, b = rnd_bytes(1 << 20), torch.zeros(1 << 20, dtype=torch.uint8, device="cuda")
