@@ -50,9 +50,17 @@ def main():
     ap.add_argument("--sort-chunk", type=int, default=1 << 23)
     ap.add_argument("--hbm-frac", type=float, default=0.5, help="fraction of the sort's data allowed in peer HBM; rest spills to host")
     ap.add_argument("--dsort-keys", type=int, default=1 << 24)      # 128 MiB of keys per rank, one global order
-    ap.add_argument("--only", choices=["dsort"], default=None, help="run just this section")
+    ap.add_argument("--only", choices=["dsort", "oocsort"], default=None, help="run just this section")
+    ap.add_argument("--sort-final", default="merge", choices=["merge", "sort", "both"])
+    ap.add_argument("--sort-parts", type=int, default=0, help="partitions per rank (0: one per run)")
+    ap.add_argument("--gpu-bytes", type=str, default="8G")
+    ap.add_argument("--host-bytes", type=str, default="3G")
     args = ap.parse_args()
-    tc = TorchrunCluster(gpu_bytes=8 << 30, host_bytes=3 << 30)
+
+    def size(s):
+        return int(float(s[:-1]) * {"K": 1 << 10, "M": 1 << 20, "G": 1 << 30, "T": 1 << 40}[s[-1].upper()]) if s[-1].isalpha() else int(s)
+
+    tc = TorchrunCluster(gpu_bytes=size(args.gpu_bytes), host_bytes=size(args.host_bytes))
     with tc as (rank, world):
         # ---- config 3 ------------------------------------------------------------------------
         tc.barrier()
@@ -82,18 +90,29 @@ def main():
         # ---- config 4 ------------------------------------------------------------------------
         tc.barrier()
         # half of the runs (and of the output) fit the HBM budget, the rest spills to the pinned host tier
-        if not args.only:
-            s = sort.run(total_keys=args.sort_keys, chunk_keys=args.sort_chunk,
-                         gpu_budget_total=int(args.hbm_frac * args.sort_keys * 8))
-            tc.barrier()
-            worst = allmax(s["seconds"], world)
-            ok = allsum(1.0 if s["ok"] else 0.0, world) == world
-        if rank == 0 and not args.only:
-            print(json.dumps({"kind": "ooc_sort", "n_gpus": world, "keys_per_rank": args.sort_keys,
-                              "bytes_per_rank": args.sort_keys * 8, "seconds_max": round(worst, 4),
-                              "Mkeys_per_s_aggregate": round(world * args.sort_keys / worst / 1e6, 1),
-                              "bytes_in_hbm_rank0": s["bytes_in_hbm"], "bytes_in_host_rank0": s["bytes_in_host"],
-                              "verified": ok}), flush=True)
+        # (runs + output: 2 x the data; --hbm-frac of that may sit in peer HBM)
+        if not args.only or args.only == "oocsort":
+            from oncilla_b200.models import oocsort
+
+            for final in (["merge", "sort"] if args.sort_final == "both" else [args.sort_final]):
+                s = oocsort.run(keys_per_rank=args.sort_keys, chunk_keys=args.sort_chunk, parts_per_rank=args.sort_parts or None,
+                                hbm_budget=int(args.hbm_frac * 2 * args.sort_keys * 8), final=final)
+                tc.barrier()
+                worst = allmax(s["seconds"], world)
+                p1, p2 = allmax(s["phase1_s"], world), allmax(s["phase2_s"], world)
+                ok = allsum(1.0 if s["ok"] else 0.0, world) == world
+                if rank == 0:
+                    print(json.dumps({"kind": "ooc_sort", "n_gpus": world, "keys_per_rank": args.sort_keys, "final": final,
+                                      "total_bytes": world * args.sort_keys * 8, "chunk_keys": args.sort_chunk,
+                                      "runs_per_rank": s["n_runs"], "slices_per_partition": s["slices_per_partition"],
+                                      "seconds_max": round(worst, 4), "phase1_run_formation_s": round(p1, 4),
+                                      "phase2_gather_merge_s": round(p2, 4),
+                                      "Mkeys_per_s_aggregate": round(world * args.sort_keys / worst / 1e6, 1),
+                                      "GBps_aggregate": round(world * args.sort_keys * 8 / worst / 1e9, 2),
+                                      "bytes_in_hbm_rank0": s["bytes_in_hbm"], "bytes_in_host_rank0": s["bytes_in_host"],
+                                      "verified": ok}), flush=True)
+        if args.only == "oocsort":
+            return
         # ---- distributed sample sort: all ranks sort one data set, keys exchanged by one-sided puts into
         # shared blocks (ocm_share / ocm_attach) with completion signals ------------------------------------
         from oncilla_b200.models import dsort

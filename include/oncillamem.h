@@ -225,6 +225,9 @@ struct ocm_stats {
     uint64_t copies, copy_bytes, kernel_launches;
     uint64_t fast_path_allocs, slow_path_allocs;
     uint64_t pool_gpu_bytes, pool_gpu_used, pool_host_bytes, pool_host_used;
+    /* granules taken out of each pool (what the blocks really cost: pool_*_used rounds every block up to its size
+     * class, these also count the free remainder of slabs) and audits that found a rank's tables inconsistent */
+    uint64_t pool_gpu_granule_bytes, pool_host_granule_bytes, table_faults;
 };
 int ocm_get_stats(struct ocm_stats *out);            /* this process + its rank's pools */
 int ocm_get_rank_stats(int rank, struct ocm_stats *out); /* via MSG_STATS to the daemon */

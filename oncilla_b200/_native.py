@@ -103,7 +103,7 @@ class ocm_stats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "allocs_live", "allocs_total", "frees_total", "bytes_gpu_live", "bytes_host_live", "copies", "copy_bytes",
         "kernel_launches", "fast_path_allocs", "slow_path_allocs", "pool_gpu_bytes", "pool_gpu_used",
-        "pool_host_bytes", "pool_host_used")]
+        "pool_host_bytes", "pool_host_used", "pool_gpu_granule_bytes", "pool_host_granule_bytes", "table_faults")]
 
 
 class ocmk_strided(C.Structure):

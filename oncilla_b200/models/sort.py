@@ -68,75 +68,15 @@ def _gen(chunk_index: int, n: int, device):
 
 
 def run(total_keys: int = 1 << 24, chunk_keys: int = 1 << 21, gpu_budget_per_rank: int = 1 << 62,
-        check: bool = True, gpu_budget_total: int | None = None) -> dict:
-    """Sort ``total_keys`` keys using working buffers of ``chunk_keys`` keys.  Returns timings and placement."""
-    import torch
+        check: bool = True, gpu_budget_total: int | None = None, final: str = "merge") -> dict:
+    """One process sorts ``total_keys`` keys alone with working buffers of ``chunk_keys`` keys: the single-rank form of
+    the pipeline in :mod:`oncilla_b200.models.oocsort` (two streams, runs put while the next one is sorted, partitions
+    merged from sorted slices).  ``gpu_budget_total`` bytes of runs + output may live in peer HBM, the rest spills to
+    the pinned host tier."""
+    from . import oocsort
 
-    dev = torch.device(f"cuda:{api.device()}")
-    n_runs = (total_keys + chunk_keys - 1) // chunk_keys
-    n_parts = n_runs
-    run_bytes = chunk_keys * 8
-    spill = _Spill(gpu_budget_per_rank, gpu_budget_total)
-    out_spill = _Spill(gpu_budget_per_rank, gpu_budget_total)
-    tiers = {"hbm": 0, "host": 0}
-    t_start = time.time()
-    # local working set: one OCM window (GPU) big enough for a run / a gathered partition (2x slack)
-    work = api.alloc(N.OCM_LOCAL_GPU, 2 * run_bytes)
-    tmp = api.alloc(N.OCM_LOCAL_GPU, 2 * run_bytes)
-    wt, tt = work.local_tensor(torch.int64), tmp.local_tensor(torch.int64)
-    try:
-        # splitters from a sample of the synthetic stream (uniform keys -> near-equal partitions)
-        sample = torch.cat([_gen(c, 1024, dev) for c in range(n_runs)])
-        ss = torch.sort(sample).values
-        splitters = ss[torch.arange(1, n_parts, device=dev) * (ss.numel() // n_parts)] if n_parts > 1 else ss[:0]
-        runs, bounds, in_sum = [], [], 0
-        for c in range(n_runs):
-            n = min(chunk_keys, total_keys - c * chunk_keys)
-            wt[:n].copy_(_gen(c, n, dev))
-            if check:
-                in_sum = (in_sum + ops.checksum(wt[:n])) & (2**64 - 1)
-            ops.sort_u64(wt[:n], tt[:n])
-            b = torch.searchsorted(wt[:n], splitters).tolist()
-            bounds.append([0] + b + [n])
-            home, tier = spill.place(n * 8)
-            tiers[tier] += n * 8
-            # K1: local HBM -> far side (peer HBM over NVLink or pinned host)
-            api.copy(home, work, n * 8, op_flag=1, stream="sync")
-            runs.append((home, n))
-        t_runs = time.time()
-        outs, out_sum, last_max, sorted_ok = [], 0, -1, True
-        for p in range(n_parts):
-            fill = 0
-            for (home, _n), b in zip(runs, bounds):
-                lo, hi = b[p], b[p + 1]
-                if hi > lo:
-                    if (fill + hi - lo) * 8 > 2 * run_bytes:
-                        raise RuntimeError("partition exceeds the working buffer; use more partitions")
-                    # K2: slice of a far side -> local window at an offset
-                    api.copy(work, home, (hi - lo) * 8, src_offset=lo * 8, dest_offset=fill * 8, op_flag=1)
-                    fill += hi - lo
-            if fill == 0:
-                outs.append((None, 0))
-                continue
-            ops.sort_u64(wt[:fill], tt[:fill])
-            if check:
-                part = wt[:fill]
-                sorted_ok &= bool((part[1:] >= part[:-1]).all().item()) and int(part[0].item()) >= last_max
-                last_max = int(part[-1].item())
-                out_sum = (out_sum + ops.checksum(part)) & (2**64 - 1)
-            dst, tier = out_spill.place(fill * 8)
-            api.copy(dst, work, fill * 8, op_flag=1)
-            outs.append((dst, fill))
-        torch.cuda.synchronize()
-        t_end = time.time()
-        total_out = sum(n for _, n in outs)
-        return {"total_keys": total_keys, "n_runs": n_runs, "seconds": t_end - t_start,
-                "phase1_s": t_runs - t_start, "phase2_s": t_end - t_runs,
-                "mkeys_per_s": total_keys / (t_end - t_start) / 1e6, "bytes_in_hbm": tiers["hbm"],
-                "bytes_in_host": tiers["host"],
-                "ok": (not check) or (sorted_ok and out_sum == in_sum and total_out == total_keys)}
-    finally:
-        work.free()
-        tmp.free()
-        spill.free()
-        out_spill.free()
+    budget = gpu_budget_total * 2 if gpu_budget_total is not None else gpu_budget_per_rank
+    r = oocsort.run(keys_per_rank=total_keys, chunk_keys=chunk_keys, hbm_budget=budget, final=final, check=check,
+                    collaborate=False)
+    r["total_keys"] = total_keys
+    return r

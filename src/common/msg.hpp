@@ -97,6 +97,7 @@ struct StatsPayload {
     uint64_t allocs_live, allocs_total, frees_total;
     uint64_t pool_bytes[TIER_COUNT], pool_used[TIER_COUNT];
     uint64_t apps, msgs_in, msgs_out, reclaimed_regions, scrubbed_bytes;
+    uint64_t pool_granule_bytes[TIER_COUNT];   // granules taken (slab remainders included)
     uint64_t table_faults;      // audits that found the rank's tables inconsistent (daemon.cpp, audit_tables)
 };
 

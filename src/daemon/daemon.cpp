@@ -784,6 +784,7 @@ void Daemon::fill_stats(StatsPayload *s) {
     for (int t = 0; t < TIER_COUNT; ++t) {
         PoolDesc &p = tbl_->pool[t];
         s->pool_bytes[t] = p.bytes;
+        s->pool_granule_bytes[t] = p.used_bytes.load(std::memory_order_relaxed);
         s->pool_used[t] = pool_payload_bytes(tbl_, t);   // what applications hold (empty cached slabs are free space)
         s->allocs_live += p.live.load(std::memory_order_relaxed);
         s->allocs_total += p.total_allocs.load(std::memory_order_relaxed);

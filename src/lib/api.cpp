@@ -1065,6 +1065,8 @@ int ocm_get_stats(struct ocm_stats *out) {
         out->pool_gpu_used = pool_payload_bytes(v->hdr, TIER_GPU);
         out->pool_host_bytes = v->hdr->pool[TIER_HOST].bytes;
         out->pool_host_used = pool_payload_bytes(v->hdr, TIER_HOST);
+        out->pool_gpu_granule_bytes = v->hdr->pool[TIER_GPU].used_bytes.load();
+        out->pool_host_granule_bytes = v->hdr->pool[TIER_HOST].used_bytes.load();
     }
     return 0;
 }
@@ -1086,6 +1088,9 @@ int ocm_get_rank_stats(int rank, struct ocm_stats *out) {
     out->pool_gpu_used = s.pool_used[TIER_GPU];
     out->pool_host_bytes = s.pool_bytes[TIER_HOST];
     out->pool_host_used = s.pool_used[TIER_HOST];
+    out->pool_gpu_granule_bytes = s.pool_granule_bytes[TIER_GPU];
+    out->pool_host_granule_bytes = s.pool_granule_bytes[TIER_HOST];
+    out->table_faults = s.table_faults;
     return 0;
 }
 

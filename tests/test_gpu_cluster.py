@@ -567,8 +567,12 @@ def test_workloads_gups_and_sort(gpu_cluster):
 
     res = gups.run(total_words=1 << 22, n_updates=1 << 22, iters=2)
     assert res["verified"] is True and res["gups"] > 0
+    res = gups.run(total_words=1 << 22, n_updates=1 << 22, iters=1, local_only=True)
+    assert res["verified"] is True and res["n_ranks"] == 1
     res = sort.run(total_keys=1 << 20, chunk_keys=1 << 18)
-    assert res["ok"] and res["n_runs"] == 4
+    assert res["ok"] and res["n_runs"] == 4 and res["final"] == "merge"
+    res = sort.run(total_keys=(1 << 20) + 777, chunk_keys=1 << 18, final="sort")
+    assert res["ok"] and res["n_runs"] == 5
     # force the host tier: HBM budget of one run per rank
     res = sort.run(total_keys=1 << 20, chunk_keys=1 << 18, gpu_budget_per_rank=(1 << 18) * 8)
     assert res["ok"] and res["bytes_in_host"] > 0
@@ -598,6 +602,16 @@ def test_distributed_sort_single_rank_and_torchrun(gpu_cluster):
 
     out = json.loads(line)
     assert out["verified"] is True and out["n_gpus"] == n
+    # the out-of-core pipeline as a job of n ranks: runs in everybody's pools, slices fetched through attached handles,
+    # half of the data forced onto the pinned host tier
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+                        "--master-addr", "127.0.0.1", "--master-port", "29633", str(REPO / "bench" / "workloads.py"),
+                        "--only", "oocsort", "--sort-keys", str(1 << 21), "--sort-chunk", str(1 << 19), "--sort-final", "both",
+                        "--gpu-bytes", "1G", "--host-bytes", "512M"], env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    lines = [json.loads(l) for l in r.stdout.splitlines() if '"ooc_sort"' in l]
+    assert [l["final"] for l in lines] == ["merge", "sort"] and all(l["verified"] is True for l in lines), lines
+    assert lines[0]["bytes_in_host_rank0"] > 0 and lines[0]["slices_per_partition"] == 4 * n
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
