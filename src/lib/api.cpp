@@ -213,8 +213,6 @@ RankView *get_view(int rank, bool with_gpu) {
             DeviceGuard dg(c.device);
             // device-visible tables (signals) and zero-copy-capable host pool
             if (!gpu::host_register(v->tbl_map.base, v->tbl_map.bytes, &err)) LOGW("%s", err.c_str());
-            if (v->host_map.base && !gpu::host_register(v->host_map.base, v->host_map.bytes, &err))
-                LOGW("%s", err.c_str());
         }
         v->ok = true;
     }
@@ -226,10 +224,24 @@ RankView *get_view(int rank, bool with_gpu) {
     return v;
 }
 
+// A rank's pinned host pool becomes device-visible for THIS process when its first block is used: registering
+// (page-locking + mapping) costs time in proportion to the pool, and an application that only touches a rank's HBM
+// never needs it (8 ranks x 24 GiB of host pool would be 192 GiB to pin per process).
+static void view_host_ready(RankView *v) {
+    Ctx &c = ctx();
+    if (!v || !v->host_map.base || c.device < 0) return;
+    std::lock_guard<std::mutex> g(c.mu);
+    if (v->host_registered) return;
+    v->host_registered = true;
+    DeviceGuard dg(c.device);
+    std::string err;
+    if (!gpu::host_register(v->host_map.base, v->host_map.bytes, &err)) LOGW("%s", err.c_str());
+}
+
 static void drop_view(RankView &v) {
     if (v.gpu.ptr) gpu::pool_release(&v.gpu);
     if (v.host_map.base) {
-        gpu::host_unregister(v.host_map.base);
+        if (v.host_registered) gpu::host_unregister(v.host_map.base);
         shm_close(&v.host_map, false);
     }
     if (v.tbl_map.base) {
@@ -310,6 +322,7 @@ static int alloc_side(uint32_t type, uint64_t bytes, int policy, int explicit_ra
         c.n_slow.fetch_add(1, std::memory_order_relaxed);
     }
     RankView *v = get_view(a.remote_rank, a.tier == TIER_GPU);
+    if (a.tier == TIER_HOST) view_host_ready(v);
     out->backing = SIDE_POOL;
     out->tier = (uint8_t)a.tier;
     out->via_daemon = slow;
@@ -992,6 +1005,7 @@ int ocm_attach(const struct ocm_share_token *tok, ocm_alloc_t *out) {
     if (tok->tier == TIER_GPU && c.device < 0) return -OCM_ENOGPU;
     RankView *v = get_view(tok->rank, tok->tier == TIER_GPU);
     if (!v) return -OCM_ENODAEMON;
+    if (tok->tier == TIER_HOST) view_host_ready(v);
     Region *rec = table_region_rec(v->hdr, (int)tok->tier, tok->region);
     if (!rec) return -OCM_EINVAL;
     // count ourselves in first, then check that the block is (still) the one the token names
