@@ -54,7 +54,7 @@ struct ocmk_strided {
 };
 int ocmk_strided_copy(const struct ocmk_strided *d, uint64_t *signal, void *stream);
 
-/* K6 replicated put: one source to n_dst destinations (cluster-shared tiles). */
+/* K6 replicated put: one source to n_dst destinations (one CTA of a cluster per destination, TMA bulk tiles). */
 int ocmk_put_replicated(void *const *dsts, int n_dst, const void *src, size_t bytes, void *stream);
 
 /* K7 GUPS over a table striped across n_ranks slabs. */

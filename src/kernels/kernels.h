@@ -83,10 +83,12 @@ __host__ __device__
 inline size_t dtype_size(int dt) { return dt == DT_F32 ? 4 : dt == DT_BF16 ? 2 : 1; }
 
 // ---- K6: replicated put ---------------------------------------------------------
-// One source, n_dst destinations (same bytes): a thread-block cluster shares
-// each staged tile (TMA cluster multicast) and every CTA stores to one replica.
+// One source, n_dst destinations (same bytes): one CTA of a thread-block cluster per replica.
+// src_on_this_gpu = the caller KNOWS src is in the launching GPU's own memory: the cluster then shares each staged
+// tile (TMA cluster multicast, the source is read once).  Otherwise every CTA loads the tile itself.
 cudaError_t launch_put_replicated(void *const *dsts, int n_dst, const void *src, size_t bytes,
-                                  uint64_t *const *signals, unsigned *ticket, cudaStream_t stream);
+                                  uint64_t *const *signals, unsigned *ticket, cudaStream_t stream,
+                                  bool src_on_this_gpu = false);
 // NVLS variant: one multimem.st stream to a multicast VA.
 cudaError_t launch_put_multimem(void *mc_dst, const void *src, size_t bytes, uint64_t *mc_signal, unsigned *ticket,
                                 cudaStream_t stream);

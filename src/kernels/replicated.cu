@@ -8,6 +8,9 @@
 //     whole tile after issuing 1/C of the reads; CTA r then bulk-stores the
 //     tile to replica r (a peer GPU over NVLink).  Stage recycling is a
 //     cluster-wide empty barrier (remote mbarrier arrives through DSMEM).
+//     This form is taken only when the caller knows the source is in the
+//     launching GPU's own memory; for any other source every CTA bulk-loads
+//     the whole tile itself (template argument MC below).
 // (b) NVLS: with a multicast virtual address the NVSwitch replicates a single
 //     multimem.st stream to every bound GPU.
 #include "kernels.h"
@@ -29,6 +32,11 @@ struct RepArgs {
     int            n_dst;
 };
 
+// MC: the cluster shares each tile with multicast loads.  Only for a source in THIS GPU's own memory: TMA multicast
+// loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU.
+// Any other source (a peer's memory, pinned host memory, unknown) takes MC = false: every CTA loads the whole tile
+// itself with plain bulk copies and no CTA depends on another one's loads.
+template <bool MC>
 __global__ void __launch_bounds__(128, 1) ocm_put_replicated_kernel(RepArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full[kRepStages];
@@ -61,6 +69,10 @@ __global__ void __launch_bounds__(128, 1) ocm_put_replicated_kernel(RepArgs a) {
             const uint32_t len = tile_len(j);
             // every CTA will receive the whole tile, a slice from each cluster member
             mbar_arrive_expect_tx(&full[s], len);
+            if (!MC) {
+                bulk_g2s(smem + (size_t)s * kRepTile, a.src + tile_off(j), len, &full[s]);
+                return;
+            }
             const uint32_t slice = ((len + C - 1) / C + 15) & ~15u;
             const uint32_t off = r * slice;
             if (off < len) {
@@ -79,10 +91,12 @@ __global__ void __launch_bounds__(128, 1) ocm_put_replicated_kernel(RepArgs a) {
                 // store i-1 has drained its stage: tell the whole cluster, then refill it
                 bulk_wait_read<1>();
                 const uint32_t ps = (uint32_t)((i - 1) % kRepStages);
-                for (uint32_t c = 0; c < C; ++c) mbar_arrive_remote(&empty[ps], c);
+                if (MC)
+                    for (uint32_t c = 0; c < C; ++c) mbar_arrive_remote(&empty[ps], c);
                 const uint64_t j = i - 1 + kRepStages;
                 if (j < n_my) {
-                    mbar_wait(&empty[ps], (uint32_t)(((j / kRepStages) - 1) & 1));
+                    // shared tiles: every CTA of the cluster must have drained the stage; private tiles: ours has
+                    if (MC) mbar_wait(&empty[ps], (uint32_t)(((j / kRepStages) - 1) & 1));
                     issue_load(j);
                 }
             }
@@ -154,7 +168,7 @@ cudaError_t launch_signal_multimem(uint64_t *mc_signal, cudaStream_t stream) {
 }
 
 cudaError_t launch_put_replicated(void *const *dsts, int n_dst, const void *src, size_t bytes,
-                                  uint64_t *const *signals, unsigned *ticket, cudaStream_t stream) {
+                                  uint64_t *const *signals, unsigned *ticket, cudaStream_t stream, bool src_on_this_gpu) {
     if (n_dst < 1 || n_dst > kRepMaxDst) return cudaErrorInvalidValue;
     if (!bytes) return cudaSuccess;
     uintptr_t al = (uintptr_t)src;
@@ -176,7 +190,9 @@ cudaError_t launch_put_replicated(void *const *dsts, int n_dst, const void *src,
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 64 && !attr[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(ocm_put_replicated_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(ocm_put_replicated_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(ocm_put_replicated_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         attr[dev] = true;
     }
@@ -192,7 +208,8 @@ cudaError_t launch_put_replicated(void *const *dsts, int n_dst, const void *src,
     at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, ocm_put_replicated_kernel, a);
+    return src_on_this_gpu ? cudaLaunchKernelEx(&cfg, ocm_put_replicated_kernel<true>, a)
+                           : cudaLaunchKernelEx(&cfg, ocm_put_replicated_kernel<false>, a);
 }
 
 // (c) NVLS gather-reduce: dst[i] = sum over all GPUs bound to the multicast object of their replica's

@@ -327,6 +327,24 @@ static void mark_pending(ocm_alloc_t a, void *stream, bool used) {
 // the ranks (the "allocations composed of partitioned distributed allocations" the reference only plans,
 // ref src/lib.c:42-45).  REPLICATED: every rank holds a full copy; a put reaches all of them in one pass
 // (cluster-multicast kernel K6), a get reads the nearest replica.
+// True only when the bytes are KNOWN to live in the HBM of the GPU this context launches on: a block of a pool whose
+// table names this GPU, or the library's own cudaMalloc on it, and the driver agrees about the pointer.  The
+// replicated put shares its source tiles across a cluster with TMA multicast only then; TMA multicast loads here
+// read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU.
+static bool source_on_this_gpu(const Side &s, uint64_t off) {
+    Ctx &c = ctx();
+    if (c.device < 0 || s.tier != TIER_GPU) return false;
+    const bool by_table = (s.backing == SIDE_POOL && s.hdr && s.hdr->gpu_index == c.device && s.rank == c.rank) ||
+                          s.backing == SIDE_CUDAMALLOC;
+    if (!by_table) return false;
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, (const char *)s.ptr + off) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return at.type == cudaMemoryTypeDevice && at.device == c.device;
+}
+
 static int stripes_xfer(ocm_alloc_t a, bool to_far, const Side &local, uint64_t local_off, uint64_t far_off, uint64_t n,
                         void *stream, bool *used) {
     Ctx &c = ctx();
@@ -362,7 +380,8 @@ static int stripes_xfer(ocm_alloc_t a, bool to_far, const Side &local, uint64_t 
             }
             DeviceGuard dg(c.device);
             cudaError_t e = ocmk::launch_put_replicated(dsts, (int)N, (const char *)local.ptr + local_off, n, sigs,
-                                                        next_ticket(), (cudaStream_t)(stream ? stream : c.stream));
+                                                        next_ticket(), (cudaStream_t)(stream ? stream : c.stream),
+                                                        source_on_this_gpu(local, local_off));
             ++c.kernel_launches;
             note_other_gpu_op();
             c.n_copies.fetch_add(1, std::memory_order_relaxed);

@@ -120,7 +120,8 @@ int ocmk_strided_copy(const struct ocmk_strided *d, uint64_t *signal, void *stre
 
 int ocmk_put_replicated(void *const *dsts, int n_dst, const void *src, size_t bytes, void *stream) {
     ++g_abi_launches;
-    return ret(ocmk::launch_put_replicated(dsts, n_dst, src, bytes, nullptr, abi_ticket(), (cudaStream_t)stream),
+    // raw pointers: where src lives is not known here, so the tiles are not shared across the cluster
+    return ret(ocmk::launch_put_replicated(dsts, n_dst, src, bytes, nullptr, abi_ticket(), (cudaStream_t)stream, false),
                "ocmk_put_replicated");
 }
 

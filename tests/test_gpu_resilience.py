@@ -197,3 +197,36 @@ a.free(); ocm.tini()
 print("BEYOND 4 GIB OK")
 """
         assert "BEYOND 4 GIB OK" in _ok(run_py(cl, 0, code, timeout=300))
+
+
+REPL_NO_NVLS = r"""
+import torch, oncilla_b200 as ocm
+from oncilla_b200 import ops
+ocm.init()
+assert not ocm.multicast_ready(0.3)
+N = ocm.num_ranks()
+for n in (4096, (5 << 20) + 48):
+    rp = ocm.alloc(ocm.OCM_REPLICATED_GPU, n, n)
+    pat = 0x7E57000000000000 | n
+    ops.fill(rp.local_tensor(), pat); torch.cuda.synchronize()
+    rp.put(n)                                                       # source = our own pool: cluster-shared tiles
+    for r in range(N):
+        assert ops.verify(rp.slab_tensor(r)[:n], pat, n) == 0, (n, r)
+    far = ocm.alloc(ocm.OCM_REMOTE_GPU, n, n)                       # far side in the neighbour's HBM
+    ops.fill(far.local_tensor(), pat ^ 0xABCD); torch.cuda.synchronize(); far.put(n)
+    dsts = [rp.slab_tensor(r)[:n] for r in range(N)]
+    ops.put_replicated(dsts, far.remote_tensor()[:n], n)            # source = a peer's memory: per-CTA loads
+    torch.cuda.synchronize()
+    for r in range(N):
+        assert ops.verify(rp.slab_tensor(r)[:n], pat ^ 0xABCD, n) == 0, (n, r)
+    rp.free(); far.free()
+ocm.tini()
+print("REPLICATED WITHOUT NVLS OK")
+"""
+
+
+def test_replicated_put_without_nvls_local_and_peer_source():
+    """OCM_MC_BYTES=0 keeps the NVLS region out, so OCM_REPLICATED_GPU puts run the cluster kernel (K6a): from this
+    GPU's own pool, and - through the kernel ABI - with a source that lives in the neighbour's HBM."""
+    with _cluster(gpu_bytes=256 << 20, host_bytes=32 << 20, extra_env={"OCM_MC_BYTES": "0"}) as cl:
+        assert "REPLICATED WITHOUT NVLS OK" in _ok(run_py(cl, 0, REPL_NO_NVLS))
