@@ -44,6 +44,8 @@ Daemon::~Daemon() {
     if (cluster_) cluster_->mc_state.store(MC_NONE);
     if (mc_.handle) gpu::mc_release(&mc_);
     if (cluster_peer_map_.base) shm_close(&cluster_peer_map_, false);
+    for (auto &p : peer_tbl_)
+        if (p.map.base) shm_close(&p.map, false);
     if (gpu_pool_.ptr) {
         if (scrub_stream_) cudaStreamDestroy((cudaStream_t)scrub_stream_);
         gpu::pool_release(&gpu_pool_);
@@ -170,6 +172,7 @@ int Daemon::setup_pools() {
     if (gpu_ >= 0) gpu::get_uuid(gpu_, tbl_->gpu_uuid);
     if (getenv("OCM_NO_SCRUB")) tbl_->scrub_enabled.store(0);
     if (getenv("OCM_NO_SLABS")) tbl_->slabs_enabled.store(0);
+    if (const char *e = getenv("OCM_DAEMON_NODE_LOCAL")) node_local_ = atoi(e) != 0;
 
     if (host_bytes) {
         if (!shm_create(shm_host_pool_name(rank_), tbl_->pool[TIER_HOST].bytes, true, &host_map_, &err)) {
@@ -656,10 +659,13 @@ void Daemon::start_alloc(Message &m) {
     m.rank = rank_;
     m.u.req.orig_rank = rank_;
     if (!joined_) return finish_alloc(m, OCM_ENODAEMON);
-    if (rank_ == 0) {
+    // rank 0 owns the cluster table; a daemon on rank 0's node sees the same table in shared memory and places the
+    // request there itself (the reservation is one CAS loop, safe from any process)
+    ClusterTable *ct = rank_ == 0 ? cluster_ : (node_local_ ? shared_cluster() : nullptr);
+    if (ct) {
         AllocRequest req = m.u.req;
         Allocation a;
-        int err = governor_place(cluster_, req, &a);
+        int err = governor_place(ct, req, &a);
         if (err) return finish_alloc(m, err);
         m.u.alloc = a;
         return placed(m);
@@ -680,6 +686,22 @@ void Daemon::placed(Message &m) {
         int err = do_alloc_local(m);
         if (err) note_free(a.remote_rank, (int)a.tier, a.bytes);
         return finish_alloc(m, err);
+    }
+    if (TableHeader *pt = peer_table(a.remote_rank)) {
+        BlockRef b;
+        if (inject_alloc_fault()) {
+            note_free(a.remote_rank, (int)a.tier, a.bytes);
+            return finish_alloc(m, OCM_ENOMEM);
+        }
+        if (a.tier < TIER_COUNT && pool_alloc(pt, (int)a.tier, a.bytes, m.pid, m.rank, &b) == OCM_OK) {
+            a.rem_alloc_id = b.id;
+            a.offset = b.offset;
+            a.block_bytes = b.block_bytes;
+            a.region = b.region;
+            a.generation = b.generation;
+            return finish_alloc(m, 0);
+        }
+        // full (maybe only until its scrubber has run), or a refused request: let the owner decide and wait
     }
     Message q = m;
     q.type = MSG_DO_ALLOC;
@@ -703,17 +725,50 @@ void Daemon::finish_alloc(Message &m, int err) {
     reply_app(m);
 }
 
-// Owner-side fulfilment (reference alloc_ate, src/alloc.c:150-222): pure table work.
-int Daemon::do_alloc_local(Message &m) {
-    Allocation &a = m.u.alloc;
-    if (a.tier >= TIER_COUNT) return OCM_EINVAL;
-    // fault injection for tests: OCM_FAULT_ALLOC_EVERY=N makes every N-th fulfilment fail
+// fault injection for tests: OCM_FAULT_ALLOC_EVERY=N makes every N-th fulfilment fail
+bool Daemon::inject_alloc_fault() {
     static const long fault_every = getenv("OCM_FAULT_ALLOC_EVERY") ? atol(getenv("OCM_FAULT_ALLOC_EVERY")) : 0;
     static long fault_count = 0;
     if (fault_every > 0 && ++fault_count % fault_every == 0) {
         LOGW("fault injection: failing allocation %ld", fault_count);
-        return OCM_ENOMEM;
+        return true;
     }
+    return false;
+}
+
+// The tables of another rank of this node, or nullptr (other node, not up yet, restarted and not yet back).
+TableHeader *Daemon::peer_table(int rank) {
+    if (!node_local_ || rank < 0 || rank >= n_ranks_ || rank >= kMaxRanks || rank == rank_) return nullptr;
+    ClusterTable *ct = shared_cluster();
+    if (!ct || !ct->node[rank].joined.load(std::memory_order_acquire)) return nullptr;
+    PeerTable &p = peer_tbl_[rank];
+    if (p.hdr && p.hdr->daemon_pid != ct->node[rank].daemon_pid) {   // that daemon was restarted: new segment, same name
+        shm_close(&p.map, false);
+        p = PeerTable();
+    }
+    if (p.hdr) return p.hdr;
+    const uint64_t now = now_ns();
+    if (now < p.retry_ns) return nullptr;
+    p.retry_ns = now + 200000000ull;
+    std::string err;
+    if (!shm_open_existing(shm_table_name(rank), &p.map, &err)) return nullptr;
+    auto *h = static_cast<TableHeader *>(p.map.base);
+    if (!table_validate(h, p.map.bytes) || h->rank != rank || h->daemon_pid != ct->node[rank].daemon_pid ||
+        !h->ready.load(std::memory_order_acquire)) {
+        shm_close(&p.map, false);
+        p.map = ShmMapping();
+        return nullptr;
+    }
+    p.hdr = h;
+    LOGI("rank %d shares this node: its requests are served from the shared tables", rank);
+    return h;
+}
+
+// Owner-side fulfilment (reference alloc_ate, src/alloc.c:150-222): pure table work.
+int Daemon::do_alloc_local(Message &m) {
+    Allocation &a = m.u.alloc;
+    if (a.tier >= TIER_COUNT) return OCM_EINVAL;
+    if (inject_alloc_fault()) return OCM_ENOMEM;
     BlockRef b;
     int err = pool_alloc(tbl_, (int)a.tier, a.bytes, m.pid, m.rank, &b);
     // blocks waiting to be zeroed still hold their space: give the scrubber a bounded moment
@@ -738,8 +793,8 @@ int Daemon::do_free_local(const Allocation &a) {
 }
 
 void Daemon::note_free(int owner_rank, int tier, uint64_t bytes) {
-    if (rank_ == 0) {
-        governor_release(cluster_, owner_rank, tier, bytes);
+    if (ClusterTable *ct = rank_ == 0 ? cluster_ : (node_local_ ? shared_cluster() : nullptr)) {
+        governor_release(ct, owner_rank, tier, bytes);
         return;
     }
     Message n;
@@ -757,6 +812,14 @@ void Daemon::start_free(Message &m) {
     if (a.remote_rank == rank_) {
         int err = do_free_local(a);
         if (!err) note_free(rank_, (int)a.tier, a.bytes);
+        m.type = MSG_RELEASE_APP;
+        m.status = MSG_RESPONSE;
+        m.err = err;
+        return reply_app(m);
+    }
+    if (TableHeader *pt = peer_table(a.remote_rank)) {
+        int err = a.tier < TIER_COUNT ? pool_free(pt, (int)a.tier, a.region, a.rem_alloc_id) : OCM_EINVAL;
+        if (!err) note_free(a.remote_rank, (int)a.tier, a.bytes);
         m.type = MSG_RELEASE_APP;
         m.status = MSG_RESPONSE;
         m.err = err;
@@ -1102,8 +1165,21 @@ void Daemon::scrub_loop() {
 int Daemon::run() {
     LOGI("oncillamem rank %d/%d up (pid %d, ns '%s')", rank_, n_ranks_, (int)getpid(), ns_tag().c_str());
     struct epoll_event evs[32];
+    // Requests come in bursts (an application's allocation loop, the two daemon hops of one request): after any event
+    // the loop keeps looking without sleeping for a short while, so that the next message does not pay an epoll
+    // wake-up (5-20 us each, four of them on one remote allocation).  OCM_DAEMON_SPIN_US=0 sleeps at once.
+    const uint64_t spin_ns = (uint64_t)env_size("OCM_DAEMON_SPIN_US", 60) * 1000ull;
+    uint64_t hot_until = 0;
     while (!stop_.load()) {
-        int n = epoll_wait(ep_, evs, 32, 100);
+        int n = epoll_wait(ep_, evs, 32, hot_until ? 0 : 100);
+        if (n == 0 && hot_until) {
+            if (now_ns() >= hot_until) hot_until = 0;
+#if defined(__x86_64__)
+            else __builtin_ia32_pause();
+#endif
+            continue;
+        }
+        if (n > 0 && spin_ns) hot_until = now_ns() + spin_ns;
         if (n < 0 && errno == EINTR) continue;
         if (n < 0) {
             LOGE("epoll_wait: %s", strerror(errno));

@@ -123,6 +123,17 @@ class Daemon {
     uint64_t mc_bytes_ = 0, mc_tail_off_ = 0;
     bool mc_added_ = false, mc_bound_ = false, mc_done_ = false;
     ShmMapping cluster_peer_map_;
+    // Tables of the other ranks of THIS node (shared memory): requests whose owner rank is mapped here are fulfilled
+    // without a TCP hop; ranks on other nodes have no segment to open and keep the message path.
+    struct PeerTable {
+        ShmMapping map;
+        TableHeader *hdr = nullptr;
+        uint64_t retry_ns = 0;
+    };
+    PeerTable peer_tbl_[kMaxRanks];
+    bool node_local_ = true;                 // OCM_DAEMON_NODE_LOCAL=0: always use the message path
+    TableHeader *peer_table(int rank);
+    bool inject_alloc_fault();
     // set by the main thread once the multicast region is READY; the scrubber thread zeroes this rank's slice of
     // ranges whose owner died (tables.hpp: mc_owner / mc_scrubbed)
     std::atomic<ClusterTable *> mc_cluster_{nullptr};

@@ -723,3 +723,39 @@ def test_reference_format_nodefile(tmp_path):
     with ocm.LocalCluster(1, nodefile=str(nf), extra_env={"OCM_NO_GPU": "1", "OCM_HOST_BYTES": "8M"}) as cl:
         out = _ok(run_app(cl, 0, [BIN / "ocm_test", 1, "1", "1", "1"]))
         assert "pass" in out
+
+
+@pytest.mark.parametrize("node_local", ["1", "0"])
+def test_daemon_path_node_local_and_message_path(node_local):
+    """Slow-path allocations from rank 1's application: with OCM_DAEMON_NODE_LOCAL=1 its daemon places and fulfils them
+    in the shared tables of this node, with =0 the request travels rank 1 -> rank 0 (placement) -> owner (fulfilment)
+    over TCP as between nodes (reference src/main.c + src/alloc.c flow).  Same results, same accounting."""
+    env = {"OCM_NO_GPU": "1", "OCM_DAEMON_NODE_LOCAL": node_local}
+    with ocm.LocalCluster(3, host_bytes=16 << 20, extra_env=env) as cl:
+        code = r"""
+import json, time, oncilla_b200 as ocm
+ocm.init()
+held, ranks = [], set()
+for i in range(40):
+    a = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 100000 + i, flags=ocm.ALLOC_SLOW_PATH)
+    ranks.add(a.remote_rank)
+    a.local_tensor()[:16] = i
+    a.put(16)
+    held.append(a)
+mid = [ocm.stats(rank=r)["allocs_live"] for r in range(3)]
+for i, a in enumerate(held):
+    a.local_tensor()[:16] = 255
+    a.get(16)
+    assert int(a.local_tensor()[3]) == i
+    a.free()
+time.sleep(0.3)
+end = [ocm.stats(rank=r)["allocs_live"] for r in range(3)]
+used = [ocm.stats(rank=r)["pool_host_used"] for r in range(3)]
+me = ocm.stats()
+ocm.tini()
+print("RESULT " + json.dumps({"ranks": sorted(ranks), "mid": mid, "end": end, "used": used, "slow": me.get("allocs_slow", -1)}))
+"""
+        out = _ok(run_py(cl, 1, code))
+        res = json.loads(out.split("RESULT ", 1)[1])
+        assert res["ranks"] == [2], res                      # neighbour policy from rank 1
+        assert sum(res["mid"]) >= 40 and res["end"] == [0, 0, 0] and res["used"] == [0, 0, 0], res
