@@ -27,6 +27,7 @@ import oncilla_b200 as ocm  # noqa: E402
 PUT_LOOP = r"""
 import json, os, sys, time, torch, oncilla_b200 as ocm
 ocm.init()
+torch.cuda.set_device(ocm.device())      # events and synchronize() must look at the GPU the library launches on
 rows, elems, pitch = 8192, 4096, 8192
 src = ocm.alloc(ocm.OCM_LOCAL_GPU, rows * pitch * 4)
 src.local_tensor(torch.float32).normal_()

@@ -11,6 +11,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import os
 import sys
 from pathlib import Path
 
@@ -52,6 +53,7 @@ def main():
     ap.add_argument("--dsort-keys", type=int, default=1 << 24)      # 128 MiB of keys per rank, one global order
     ap.add_argument("--only", choices=["dsort", "oocsort"], default=None, help="run just this section")
     ap.add_argument("--sort-final", default="merge", choices=["merge", "sort", "both"])
+    ap.add_argument("--sort-repeat", type=int, default=1, help="passes of the out-of-core sort (the first one pays the host-pool pinning)")
     ap.add_argument("--sort-parts", type=int, default=0, help="partitions per rank (0: one per run)")
     ap.add_argument("--gpu-bytes", type=str, default="8G")
     ap.add_argument("--host-bytes", type=str, default="3G")
@@ -60,6 +62,9 @@ def main():
     def size(s):
         return int(float(s[:-1]) * {"K": 1 << 10, "M": 1 << 20, "G": 1 << 30, "T": 1 << 40}[s[-1].upper()]) if s[-1].isalpha() else int(s)
 
+    # the replicated-put section holds one 64 MiB replicated allocation per rank at once: size the NVLS region for it
+    w = int(os.environ.get("WORLD_SIZE", "1"))
+    os.environ.setdefault("OCM_MC_BYTES", str(min(1 << 30, (64 << 20) * w + (64 << 20))))
     tc = TorchrunCluster(gpu_bytes=size(args.gpu_bytes), host_bytes=size(args.host_bytes))
     with tc as (rank, world):
         # ---- config 3 ------------------------------------------------------------------------
@@ -74,9 +79,9 @@ def main():
             tc.barrier()
             worst_local = allmax(gl["seconds"], world)
         if rank == 0 and not args.only:
-            # Roofline of the pooled case: an 8-byte RED is one NVLink request of at least 32 bytes on the wire
-            # (16-byte header + payload flit), so 900 GB/s per direction carries at most ~28 G remote updates/s per GPU;
-            # (world-1)/world of the updates are remote.
+            # Roofline of the pooled case: a remote 8-byte RED crosses NVLink as 8 bytes of payload + 32 bytes of protocol
+            # (ncu nvltx__bytes_data_user / _data_protocol, profiles/nvlink_ncu_2gpu.md), so 900 GB/s per direction
+            # carries at most 22.5 G remote updates/s per GPU; (world-1)/world of the updates are remote.
             per_gpu = args.gups_updates / worst / 1e9
             remote_frac = (world - 1) / world if world > 1 else 0.0
             print(json.dumps({"kind": "gups", "n_gpus": world, "table_words_per_rank": args.gups_words,
@@ -84,8 +89,8 @@ def main():
                               "GUPS_aggregate": round(world * args.gups_updates / worst / 1e9, 3),
                               "GUPS_per_gpu": round(per_gpu, 3),
                               "GUPS_per_gpu_local_hbm_only": round(args.gups_updates / worst_local / 1e9, 3),
-                              "nvlink_packet_bound_GUPS_per_gpu": round(900.0 / 32.0 / remote_frac, 1) if remote_frac else None,
-                              "frac_of_nvlink_packet_bound": round(per_gpu * remote_frac / (900.0 / 32.0), 3) if remote_frac else None,
+                              "nvlink_packet_bound_GUPS_per_gpu": round(900.0 / 40.0 / remote_frac, 1) if remote_frac else None,
+                              "frac_of_nvlink_packet_bound": round(per_gpu * remote_frac / (900.0 / 40.0), 3) if remote_frac else None,
                               "verified": ok and bool(gl["verified"])}), flush=True)
         # ---- config 4 ------------------------------------------------------------------------
         tc.barrier()
@@ -94,7 +99,8 @@ def main():
         if not args.only or args.only == "oocsort":
             from oncilla_b200.models import oocsort
 
-            for final in (["merge", "sort"] if args.sort_final == "both" else [args.sort_final]):
+            finals = ["merge", "sort"] if args.sort_final == "both" else [args.sort_final]
+            for pass_no, final in enumerate(finals * args.sort_repeat):
                 s = oocsort.run(keys_per_rank=args.sort_keys, chunk_keys=args.sort_chunk, parts_per_rank=args.sort_parts or None,
                                 hbm_budget=int(args.hbm_frac * 2 * args.sort_keys * 8), final=final)
                 tc.barrier()
@@ -103,6 +109,7 @@ def main():
                 ok = allsum(1.0 if s["ok"] else 0.0, world) == world
                 if rank == 0:
                     print(json.dumps({"kind": "ooc_sort", "n_gpus": world, "keys_per_rank": args.sort_keys, "final": final,
+                                      "pass": pass_no,  # pass 0 also pins the host-pool pieces it touches (once per process)
                                       "total_bytes": world * args.sort_keys * 8, "chunk_keys": args.sort_chunk,
                                       "runs_per_rank": s["n_runs"], "slices_per_partition": s["slices_per_partition"],
                                       "seconds_max": round(worst, 4), "phase1_run_formation_s": round(p1, 4),

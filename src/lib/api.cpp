@@ -224,24 +224,53 @@ RankView *get_view(int rank, bool with_gpu) {
     return v;
 }
 
-// A rank's pinned host pool becomes device-visible for THIS process when its first block is used: registering
-// (page-locking + mapping) costs time in proportion to the pool, and an application that only touches a rank's HBM
-// never needs it (8 ranks x 24 GiB of host pool would be 192 GiB to pin per process).
-static void view_host_ready(RankView *v) {
+// A rank's pinned host pool becomes device-visible for THIS process piece by piece, when a block in that piece is
+// first used: registering (page-locking + mapping into this process and its GPU) costs time in proportion to the
+// bytes registered - measured ~0.5 s per GiB with eight applications doing it at once on the B200 box - and an
+// application only ever touches the blocks it allocated or attached (8 ranks x 24 GiB of host pools would be
+// 192 GiB to pin per process).  Pieces are OCM_HOST_REG_CHUNK bytes (default 64 MiB), aligned to the pool's base.
+static uint64_t host_reg_chunk() {
+    static const uint64_t v = [] {
+        const char *e = getenv("OCM_HOST_REG_CHUNK");
+        uint64_t b = e && *e ? strtoull(e, nullptr, 0) : (64ull << 20);
+        if (b < (2ull << 20)) b = 2ull << 20;
+        return (b + 4095) & ~4095ull;
+    }();
+    return v;
+}
+
+static void view_host_ready(RankView *v, uint64_t offset, uint64_t bytes) {
     Ctx &c = ctx();
-    if (!v || !v->host_map.base || c.device < 0) return;
+    if (!v || !v->host_map.base || c.device < 0 || !bytes) return;
+    const uint64_t chunk = host_reg_chunk(), total = v->host_map.bytes;
+    if (offset >= total) return;
+    if (bytes > total - offset) bytes = total - offset;
     std::lock_guard<std::mutex> g(c.mu);
-    if (v->host_registered) return;
-    v->host_registered = true;
-    DeviceGuard dg(c.device);
-    std::string err;
-    if (!gpu::host_register(v->host_map.base, v->host_map.bytes, &err)) LOGW("%s", err.c_str());
+    if (v->host_chunk_reg.empty()) v->host_chunk_reg.assign((size_t)((total + chunk - 1) / chunk), 0);
+    const size_t first = (size_t)(offset / chunk), last = (size_t)((offset + bytes - 1) / chunk);
+    for (size_t i = first; i <= last; ++i) {
+        if (v->host_chunk_reg[i]) continue;
+        // one call for a run of unregistered chunks
+        size_t j = i;
+        while (j + 1 <= last && !v->host_chunk_reg[j + 1]) ++j;
+        const uint64_t lo = i * chunk, hi = std::min<uint64_t>((j + 1) * chunk, total);
+        DeviceGuard dg(c.device);
+        std::string err;
+        if (!gpu::host_register((char *)v->host_map.base + lo, hi - lo, &err)) LOGW("%s", err.c_str());
+        for (size_t k = i; k <= j; ++k) v->host_chunk_reg[k] = (uint8_t)(k == i ? 2 : 1);   // 2 = head of a registration
+        v->host_registered = true;
+        i = j;
+    }
 }
 
 static void drop_view(RankView &v) {
     if (v.gpu.ptr) gpu::pool_release(&v.gpu);
     if (v.host_map.base) {
-        if (v.host_registered) gpu::host_unregister(v.host_map.base);
+        if (v.host_registered) {
+            const uint64_t chunk = host_reg_chunk();
+            for (size_t i = 0; i < v.host_chunk_reg.size(); ++i)
+                if (v.host_chunk_reg[i] == 2) gpu::host_unregister((char *)v.host_map.base + i * chunk);
+        }
         shm_close(&v.host_map, false);
     }
     if (v.tbl_map.base) {
@@ -322,7 +351,7 @@ static int alloc_side(uint32_t type, uint64_t bytes, int policy, int explicit_ra
         c.n_slow.fetch_add(1, std::memory_order_relaxed);
     }
     RankView *v = get_view(a.remote_rank, a.tier == TIER_GPU);
-    if (a.tier == TIER_HOST) view_host_ready(v);
+    if (a.tier == TIER_HOST) view_host_ready(v, a.offset, a.block_bytes ? a.block_bytes : bytes);
     out->backing = SIDE_POOL;
     out->tier = (uint8_t)a.tier;
     out->via_daemon = slow;
@@ -1005,7 +1034,6 @@ int ocm_attach(const struct ocm_share_token *tok, ocm_alloc_t *out) {
     if (tok->tier == TIER_GPU && c.device < 0) return -OCM_ENOGPU;
     RankView *v = get_view(tok->rank, tok->tier == TIER_GPU);
     if (!v) return -OCM_ENODAEMON;
-    if (tok->tier == TIER_HOST) view_host_ready(v);
     Region *rec = table_region_rec(v->hdr, (int)tok->tier, tok->region);
     if (!rec) return -OCM_EINVAL;
     // count ourselves in first, then check that the block is (still) the one the token names
@@ -1016,6 +1044,7 @@ int ocm_attach(const struct ocm_share_token *tok, ocm_alloc_t *out) {
     // (a sub-block's offset is read after the liveness check: its slab cannot retire while the block is live)
     const uint64_t blk_off = live ? table_region_offset(v->hdr, (int)tok->tier, tok->region) : 0;
     void *ptr = live ? side_ptr(v, (int)tok->tier, blk_off) : nullptr;
+    if (ptr && tok->tier == TIER_HOST) view_host_ready(v, blk_off, tok->bytes);
     if (!ptr) {
         attached_dec(rec);
         return live ? (tok->tier == TIER_GPU ? -OCM_ENOGPU : -OCM_ENODAEMON) : -OCM_ESTALE;

@@ -26,7 +26,8 @@ struct RankView {
     ShmMapping   tbl_map;
     TableHeader *hdr = nullptr;
     ShmMapping   host_map;
-    bool         host_registered = false;   // pinned + mapped for our GPU (done when the first host-tier block is used)
+    bool         host_registered = false;   // at least one chunk of the host pool is pinned + mapped for our GPU
+    std::vector<uint8_t> host_chunk_reg;    // per chunk of the host pool: registered for this process (api.cpp)
     bool         gpu_tried = false;
     gpu::PoolMapping gpu;       // ptr == nullptr if the rank has no HBM pool or we have no GPU
     uint64_t     access_mask = 0;   // devices of this process that may touch `gpu` (bit = CUDA ordinal)
