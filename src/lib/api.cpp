@@ -228,21 +228,11 @@ RankView *get_view(int rank, bool with_gpu) {
 // first used: registering (page-locking + mapping into this process and its GPU) costs time in proportion to the
 // bytes registered - measured ~0.5 s per GiB with eight applications doing it at once on the B200 box - and an
 // application only ever touches the blocks it allocated or attached (8 ranks x 24 GiB of host pools would be
-// 192 GiB to pin per process).  Pieces are OCM_HOST_REG_CHUNK bytes (default 64 MiB), aligned to the pool's base.
-static uint64_t host_reg_chunk() {
-    static const uint64_t v = [] {
-        const char *e = getenv("OCM_HOST_REG_CHUNK");
-        uint64_t b = e && *e ? strtoull(e, nullptr, 0) : (64ull << 20);
-        if (b < (2ull << 20)) b = 2ull << 20;
-        return (b + 4095) & ~4095ull;
-    }();
-    return v;
-}
-
+// 192 GiB to pin per process).  Pieces: ctx.hpp host_reg_chunk (the whole pool up to 2 GiB, else 256 MiB; OCM_HOST_REG_CHUNK), aligned to the pool's base.
 static void view_host_ready(RankView *v, uint64_t offset, uint64_t bytes) {
     Ctx &c = ctx();
     if (!v || !v->host_map.base || c.device < 0 || !bytes) return;
-    const uint64_t chunk = host_reg_chunk(), total = v->host_map.bytes;
+    const uint64_t total = v->host_map.bytes, chunk = host_reg_chunk(v->hdr->pool[TIER_HOST].bytes);
     if (offset >= total) return;
     if (bytes > total - offset) bytes = total - offset;
     std::lock_guard<std::mutex> g(c.mu);
@@ -267,7 +257,7 @@ static void drop_view(RankView &v) {
     if (v.gpu.ptr) gpu::pool_release(&v.gpu);
     if (v.host_map.base) {
         if (v.host_registered) {
-            const uint64_t chunk = host_reg_chunk();
+            const uint64_t chunk = host_reg_chunk(v.hdr ? v.hdr->pool[TIER_HOST].bytes : v.host_map.bytes);
             for (size_t i = 0; i < v.host_chunk_reg.size(); ++i)
                 if (v.host_chunk_reg[i] == 2) gpu::host_unregister((char *)v.host_map.base + i * chunk);
         }

@@ -214,10 +214,23 @@ static int single_copy(const Side &dst, uint64_t dst_off, const Side &src, uint6
                                           note_kernel(signal != nullptr)),
                         "copy kernel");
     }
-    // host tier <-> GPU: copy engine (H1)
+    // host tier <-> GPU: copy engine (H1).  A block of a host pool may lie in several separately pinned pieces of the
+    // pool (ctx.hpp host_reg_chunk) and one cudaMemcpyAsync must stay inside one registration: cut at the boundaries.
     note_other_gpu_op();
-    return cuda_err(cudaMemcpyAsync(d, s, bytes, dst.tier == TIER_GPU ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost, st),
-                    "cudaMemcpyAsync");
+    const Side &h = dst.tier == TIER_HOST ? dst : src;
+    const bool pool_host = h.backing == SIDE_POOL || h.backing == SIDE_ATTACHED;
+    const uint64_t chunk = host_reg_chunk(pool_host && h.hdr ? h.hdr->pool[TIER_HOST].bytes : 0);
+    const cudaMemcpyKind kind = dst.tier == TIER_GPU ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+    uint64_t pos = h.offset + (dst.tier == TIER_HOST ? dst_off : src_off);      // position inside the pool
+    for (uint64_t done = 0; done < bytes;) {
+        uint64_t n = bytes - done;
+        if (pool_host) n = std::min<uint64_t>(n, chunk - pos % chunk);
+        int err = cuda_err(cudaMemcpyAsync(d + done, s + done, n, kind, st), "cudaMemcpyAsync");
+        if (err) return err;
+        done += n;
+        pos += n;
+    }
+    return OCM_OK;
 }
 
 // [off, off+n) lies inside the side (written so that huge offsets cannot wrap around)

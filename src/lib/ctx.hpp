@@ -8,6 +8,7 @@
 #include "../kernels/kernels.h"
 #include "../../include/oncillamem.h"
 #include <atomic>
+#include <cstdlib>
 #include <condition_variable>
 #include <unordered_map>
 #include <mutex>
@@ -83,6 +84,21 @@ struct Side {
     uint64_t *gpu_signal() const { return reinterpret_cast<uint64_t *>(sig_gpu); }
     bool valid() const { return backing != SIDE_NONE; }
 };
+
+// Size of the pieces in which a process pins a rank's host pool (api.cpp view_host_ready).  A library copy between
+// host and GPU memory must not straddle two pieces: they may be separate registrations (copy.cpp single_copy).
+inline uint64_t host_reg_chunk(uint64_t pool_bytes) {
+    static const uint64_t env = [] {
+        const char *e = getenv("OCM_HOST_REG_CHUNK");
+        uint64_t b = e && *e ? strtoull(e, nullptr, 0) : 0;
+        if (b && b < (2ull << 20)) b = 2ull << 20;
+        return (b + 4095) & ~4095ull;
+    }();
+    if (env) return env;
+    // small pools are pinned whole (one registration: any copy, also one issued by the application itself, may span
+    // the pool); large ones in 256 MiB pieces
+    return pool_bytes <= (2ull << 30) ? (pool_bytes ? ((pool_bytes + 4095) & ~4095ull) : 4096) : (256ull << 20);
+}
 
 // An attached side (ocm_attach) goes stale when the owner frees the block.
 inline bool side_stale(const Side &s) {

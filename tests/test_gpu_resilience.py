@@ -230,3 +230,40 @@ def test_replicated_put_without_nvls_local_and_peer_source():
     GPU's own pool, and - through the kernel ABI - with a source that lives in the neighbour's HBM."""
     with _cluster(gpu_bytes=256 << 20, host_bytes=32 << 20, extra_env={"OCM_MC_BYTES": "0"}) as cl:
         assert "REPLICATED WITHOUT NVLS OK" in _ok(run_py(cl, 0, REPL_NO_NVLS))
+
+
+HOST_PIECES = r"""
+import torch, oncilla_b200 as ocm
+from oncilla_b200 import ops
+ocm.init()
+dev = torch.device(f"cuda:{ocm.device()}")
+g = ocm.alloc(ocm.OCM_LOCAL_GPU, 9 << 20)
+blocks = []
+for i in range(6):                                   # 5 MiB blocks in a pool pinned in 2 MiB pieces: each spans 3-4 pieces,
+    h = ocm.alloc(ocm.OCM_REMOTE_HOST, 0, 5 << 20, flags=ocm.ALLOC_NO_WINDOW)   # registered at different times
+    blocks.append(h)
+for i, h in enumerate(blocks):
+    pat = 0xC0FFEE0000000000 | i
+    ops.fill(g.local_tensor()[: 5 << 20], pat); torch.cuda.synchronize()
+    ocm.copy(h, g, 5 << 20)                          # GPU -> host block (copy engine, cut at the piece boundaries)
+    ops.fill(g.local_tensor(), 0); torch.cuda.synchronize()
+    ocm.copy(g, h, (5 << 20) - 4096, src_offset=4096, dest_offset=8192)
+    assert ops.verify(g.local_tensor()[8192: 8192 + (5 << 20) - 4096], pat, (5 << 20) - 4096) == 0, i
+blocks[1].free(); blocks[3].free()
+big = ocm.alloc(ocm.OCM_REMOTE_HOST, 0, 9 << 20, flags=ocm.ALLOC_NO_WINDOW)     # lands across old and new pieces
+ops.fill(g.local_tensor(), 0x77); torch.cuda.synchronize()
+ocm.copy(big, g, 9 << 20)
+ops.fill(g.local_tensor(), 0); torch.cuda.synchronize()
+ocm.copy(g, big, 9 << 20)
+assert ops.verify(g.local_tensor(), 0x77, 9 << 20) == 0
+for h in (blocks[0], blocks[2], blocks[4], blocks[5], big, g): h.free()
+ocm.tini()
+print("HOST PIECES OK")
+"""
+
+
+def test_host_pool_pinned_in_pieces():
+    """OCM_HOST_REG_CHUNK=2M: a process pins a rank's host pool piece by piece as its blocks are used; blocks that span
+    pieces registered at different times still copy to and from the GPU (the library cuts its copies at the seams)."""
+    with _cluster(gpu_bytes=256 << 20, host_bytes=64 << 20) as cl:
+        assert "HOST PIECES OK" in _ok(run_py(cl, 0, HOST_PIECES, env_extra={"OCM_HOST_REG_CHUNK": str(2 << 20)}))
