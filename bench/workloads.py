@@ -117,6 +117,7 @@ def main():
                                       "Mkeys_per_s_aggregate": round(world * args.sort_keys / worst / 1e6, 1),
                                       "GBps_aggregate": round(world * args.sort_keys * 8 / worst / 1e9, 2),
                                       "bytes_in_hbm_rank0": s["bytes_in_hbm"], "bytes_in_host_rank0": s["bytes_in_host"],
+                                      "host_blocked_s_rank0": s["host_blocked_s"],
                                       "verified": ok}), flush=True)
         if args.only == "oocsort":
             return

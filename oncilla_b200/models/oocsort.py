@@ -110,6 +110,13 @@ def run(keys_per_rank: int = 1 << 22, chunk_keys: int = 1 << 20, parts_per_rank:
     tt = [t.local_tensor(torch.int64) for t in tmp]
     runs_spill, out_spill = Spill(hbm_budget // 2, rank), Spill(hbm_budget // 2, rank + 1)
     attached: list = []
+    host_s = {"place": 0.0, "copy_calls": 0.0, "control": 0.0, "splitters": 0.0}   # host time spent blocked in each kind of call
+
+    def timed(key, fn, *a, **kw):
+        t = time.perf_counter()
+        r = fn(*a, **kw)
+        host_s[key] += time.perf_counter() - t
+        return r
 
     def all_gather_obj(obj):
         if not dist:
@@ -137,6 +144,7 @@ def run(keys_per_rank: int = 1 << 22, chunk_keys: int = 1 << 20, parts_per_rank:
         ss = torch.sort(_u(samples)).values                       # signed view of the unsigned order
         spl = ss[torch.arange(1, P, device=dev) * (ss.numel() // P)] if P > 1 else ss[:0]
 
+        host_s["splitters"] = time.time() - t_start
         # ---- phase 1: run formation, two buffers / two streams -------------------------------------------------
         in_acc = torch.zeros(1, dtype=torch.int64, device=dev)
         bounds_dev = torch.zeros(n_runs, P + 1, dtype=torch.int64, device=dev)
@@ -144,7 +152,7 @@ def run(keys_per_rank: int = 1 << 22, chunk_keys: int = 1 << 20, parts_per_rank:
         for c in range(n_runs):
             b = c & 1
             n = min(chunk_keys, keys_per_rank - c * chunk_keys)
-            home, _tier = runs_spill.place(n * 8)
+            home, _tier = timed("place", runs_spill.place, n * 8)
             with torch.cuda.stream(streams[b]):
                 keys = wt[b][:n]
                 _gen_into(keys, rank, c, dev)
@@ -158,12 +166,13 @@ def run(keys_per_rank: int = 1 << 22, chunk_keys: int = 1 << 20, parts_per_rank:
                 bounds_dev[c, 1:P] = torch.searchsorted(_u(keys), spl)
                 bounds_dev[c, P] = n
                 # K1: the run leaves for its home while the other buffer is being generated and sorted
-                api.copy(home, work[b], n * 8, stream=streams[b])
+                timed("copy_calls", api.copy, home, work[b], n * 8, stream=streams[b])
             runs.append((home, n))
         barrier()
         t_runs = time.time()
 
         # ---- control plane: who holds which run, and where the splitters cut it ------------------------------------
+        t_ctl = time.perf_counter()
         my_bounds = bounds_dev.cpu().tolist()
         info = all_gather_obj({"tokens": [h.share().hex() for h, _ in runs], "bounds": my_bounds})
         sources = []                                              # (handle, bounds) of every run of every rank
@@ -176,6 +185,7 @@ def run(keys_per_rank: int = 1 << 22, chunk_keys: int = 1 << 20, parts_per_rank:
                     attached.append(h)
                 sources.append((h, bnd))
 
+        host_s["control"] = time.perf_counter() - t_ctl
         # ---- phase 2: my partitions; gets of partition q+1 overlap the merge of partition q ------------------------
         out_acc = torch.zeros(1, dtype=torch.int64, device=dev)
         ok_dev = torch.ones(1, dtype=torch.bool, device=dev)
@@ -192,7 +202,8 @@ def run(keys_per_rank: int = 1 << 22, chunk_keys: int = 1 << 20, parts_per_rank:
                         if fill + hi - lo > buf_keys:
                             raise RuntimeError("partition exceeds the working buffer: use more partitions per rank")
                         # K2: this partition's slice of a run, from wherever the run lives, to its place in the buffer
-                        api.copy(work[b], h, (hi - lo) * 8, src_offset=lo * 8, dest_offset=fill * 8, stream=streams[b])
+                        timed("copy_calls", api.copy, work[b], h, (hi - lo) * 8, src_offset=lo * 8, dest_offset=fill * 8,
+                              stream=streams[b])
                         fill += hi - lo
                         offs.append(fill)
                 sizes.append(fill)
@@ -213,9 +224,9 @@ def run(keys_per_rank: int = 1 << 22, chunk_keys: int = 1 << 20, parts_per_rank:
                     ok_dev &= (sp[1:] >= sp[:-1]).all()
                     edges[q, 0], edges[q, 1] = sp[0], sp[-1]
                     add_checksum(out_acc, part)
-                dst, _tier = out_spill.place(fill * 8)
+                dst, _tier = timed("place", out_spill.place, fill * 8)
                 src_alloc = work[b] if part.data_ptr() == wt[b].data_ptr() else tmp[b]
-                api.copy(dst, src_alloc, fill * 8, stream=streams[b])
+                timed("copy_calls", api.copy, dst, src_alloc, fill * 8, stream=streams[b])
                 outs.append(dst)
         barrier()
         t_end = time.time()
@@ -242,7 +253,8 @@ def run(keys_per_rank: int = 1 << 22, chunk_keys: int = 1 << 20, parts_per_rank:
                 "mkeys_per_s": world * keys_per_rank / seconds / 1e6,
                 "bytes_in_hbm": runs_spill.bytes["hbm"] + out_spill.bytes["hbm"],
                 "bytes_in_host": runs_spill.bytes["host"] + out_spill.bytes["host"],
-                "slices_per_partition": len(sources), "ok": bool(ok)}
+                "slices_per_partition": len(sources), "host_blocked_s": {k: round(v, 4) for k, v in host_s.items()},
+                "ok": bool(ok)}
     finally:
         torch.cuda.synchronize()
         if dist:
