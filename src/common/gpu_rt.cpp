@@ -289,6 +289,99 @@ bool pool_grant_access(const PoolMapping *m, int dev, std::string *err) {
     return true;
 }
 
+// ------------------------------------------------------------ host pool (VMM) --
+static bool map_host_handle(CUmemGenericAllocationHandle h, size_t bytes, int numa, int access_dev, void **ptr, std::string *err) {
+    CUdeviceptr va = 0;
+    CUresult r = drv().MemAddressReserve(&va, bytes, 2 << 20, 0, 0);
+    if (r != CUDA_SUCCESS) {
+        set_err(err, "cuMemAddressReserve(host pool): " + cu_str(r));
+        return false;
+    }
+    r = drv().MemMap(va, bytes, 0, h, 0);
+    if (r != CUDA_SUCCESS) {
+        drv().MemAddressFree(va, bytes);
+        set_err(err, "cuMemMap(host pool): " + cu_str(r));
+        return false;
+    }
+    CUmemAccessDesc ad[2] = {};
+    ad[0].location.type = CU_MEM_LOCATION_TYPE_HOST_NUMA;
+    ad[0].location.id = numa;
+    ad[0].flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+    ad[1].location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+    ad[1].location.id = access_dev;
+    ad[1].flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+    r = drv().MemSetAccess(va, bytes, ad, access_dev >= 0 ? 2 : 1);
+    if (r != CUDA_SUCCESS) {
+        drv().MemUnmap(va, bytes);
+        drv().MemAddressFree(va, bytes);
+        set_err(err, "cuMemSetAccess(host pool, dev " + std::to_string(access_dev) + "): " + cu_str(r));
+        return false;
+    }
+    *ptr = reinterpret_cast<void *>(va);
+    return true;
+}
+
+bool host_pool_create(int numa, size_t bytes, int access_dev, PoolMapping *out, std::string *err) {
+    if (!drv().ok || access_dev < 0) {
+        set_err(err, "CUDA driver VMM entry points unavailable");
+        return false;
+    }
+    if (!set_device(access_dev, err)) return false;
+    if (numa < 0) numa = 0;
+    CUmemAllocationProp p = {};
+    p.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+    p.location.type = CU_MEM_LOCATION_TYPE_HOST_NUMA;
+    p.location.id = numa;
+    p.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    size_t g = 0;
+    if (drv().MemGranularity(&g, &p, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED) != CUDA_SUCCESS || !g) g = 2 << 20;
+    const size_t sz = (bytes + g - 1) / g * g;
+    CUmemGenericAllocationHandle h = 0;
+    CUresult r = drv().MemCreate(&h, sz, &p, 0);
+    if (r != CUDA_SUCCESS) {
+        set_err(err, "cuMemCreate(host NUMA " + std::to_string(numa) + ", " + std::to_string(sz) + "): " + cu_str(r));
+        return false;
+    }
+    void *ptr = nullptr;
+    if (!map_host_handle(h, sz, numa, access_dev, &ptr, err)) {
+        drv().MemRelease(h);
+        return false;
+    }
+    int fd = -1;
+    r = drv().MemExport(&fd, h, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
+    if (r != CUDA_SUCCESS) {
+        set_err(err, "cuMemExportToShareableHandle(host pool): " + cu_str(r));
+        drv().MemUnmap((CUdeviceptr)ptr, sz);
+        drv().MemAddressFree((CUdeviceptr)ptr, sz);
+        drv().MemRelease(h);
+        return false;
+    }
+    out->ptr = ptr; out->bytes = sz; out->owner_dev = numa; out->access_dev = access_dev;
+    out->share_fd = fd; out->vmm_handle = (uint64_t)h; out->mode = GPU_SHARE_VMM_FD; out->imported = false;
+    return true;
+}
+
+bool host_pool_import_fd(int fd, size_t bytes, int numa, int access_dev, PoolMapping *out, std::string *err) {
+    if (!drv().ok) {
+        set_err(err, "CUDA driver VMM entry points unavailable");
+        return false;
+    }
+    CUmemGenericAllocationHandle h = 0;
+    CUresult r = drv().MemImport(&h, (void *)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+    if (r != CUDA_SUCCESS) {
+        set_err(err, "cuMemImportFromShareableHandle(host pool): " + cu_str(r));
+        return false;
+    }
+    void *ptr = nullptr;
+    if (!map_host_handle(h, bytes, numa < 0 ? 0 : numa, access_dev, &ptr, err)) {
+        drv().MemRelease(h);
+        return false;
+    }
+    out->ptr = ptr; out->bytes = bytes; out->owner_dev = numa; out->access_dev = access_dev;
+    out->share_fd = -1; out->vmm_handle = (uint64_t)h; out->mode = GPU_SHARE_VMM_FD; out->imported = true;
+    return true;
+}
+
 void pool_release(PoolMapping *m) {
     if (!m->ptr) return;
     if (m->mode == GPU_SHARE_VMM_FD && drv().ok) {

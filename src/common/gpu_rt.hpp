@@ -48,6 +48,13 @@ bool pool_import_ipc(const uint8_t ipc_handle[64], size_t bytes, int owner_dev, 
                      std::string *err);
 void pool_release(PoolMapping *m);
 // Let one more device of this process access an existing VMM mapping (same virtual address).
+// Pinned host memory as a VMM allocation (cuMemCreate, location = host NUMA node `numa`): created and pinned once by
+// the owner, shared by file descriptor like an HBM pool.  An importing process maps it in milliseconds per GiB,
+// where cudaHostRegister of a shared-memory segment pins every page again in every process (measured on the B200
+// box, 4 GiB: 0.12 s against 0.88 s; bench/hostvmm_probe.cu).  The mapping is readable and writable by `access_dev`
+// and by the CPU.  PoolMapping.owner_dev carries the NUMA node.
+bool host_pool_create(int numa, size_t bytes, int access_dev, PoolMapping *out, std::string *err);
+bool host_pool_import_fd(int fd, size_t bytes, int numa, int access_dev, PoolMapping *out, std::string *err);
 bool pool_grant_access(const PoolMapping *m, int dev, std::string *err);
 
 // ---- NVLS multicast objects (cuMulticast*) ------------------------------------------------------

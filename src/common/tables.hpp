@@ -34,7 +34,7 @@
 namespace ocm {
 
 constexpr uint64_t kTableMagic   = 0x4F434D5441424C45ull; // "OCMTABLE"
-constexpr uint32_t kTableVersion = 7;
+constexpr uint32_t kTableVersion = 8;
 constexpr uint32_t kMaxGranules  = 1u << 18;
 constexpr uint64_t kMcGranule     = 64ull << 10;
 constexpr uint32_t kMcMaxGranules = 1u << 14;     // multicast region <= 1 GiB
@@ -150,14 +150,15 @@ struct TableHeader {
     std::atomic<uint32_t> ready;       // set last by the daemon
     std::atomic<uint32_t> scrub_enabled;
     std::atomic<uint32_t> slabs_enabled;   // sub-granule size classes (OCM_NO_SLABS clears it)
-    uint32_t pad_hdr;
+    uint32_t host_share_mode;          // how applications map the host pool: GPU_SHARE_NONE = the shared-memory segment,
+                                       // GPU_SHARE_VMM_FD = pinned VMM allocation (CUDA host NUMA location), fd from the daemon
     std::atomic<uint64_t> next_id;
     std::atomic<uint64_t> heartbeat_ns; // daemon liveness (CLOCK_MONOTONIC)
     uint64_t mc_tail_offset;           // NVLS: byte offset inside the HBM pool mapping of the multicast slice
     uint64_t mc_bytes;                 //       its length (0: none)
     uint64_t sigext_offset;            // SigExt[kSigExtRecords], from segment start
     uint32_t n_sigext;
-    uint32_t pad2;
+    int32_t  host_numa_node;           // NUMA node of a VMM host pool (its CUDA memory location id)
     PoolDesc pool[TIER_COUNT];
 };
 

@@ -1,4 +1,5 @@
 #include "daemon.hpp"
+#include <sys/mman.h>
 #include "../common/governor.hpp"
 #include "../common/log.hpp"
 #include "../common/names.hpp"
@@ -49,6 +50,10 @@ Daemon::~Daemon() {
     if (gpu_pool_.ptr) {
         if (scrub_stream_) cudaStreamDestroy((cudaStream_t)scrub_stream_);
         gpu::pool_release(&gpu_pool_);
+    }
+    if (host_vmm_.ptr) {
+        gpu::pool_release(&host_vmm_);
+        host_map_ = ShmMapping();
     }
     if (host_map_.base) {
         gpu::host_unregister(host_map_.base);
@@ -174,7 +179,28 @@ int Daemon::setup_pools() {
     if (getenv("OCM_NO_SLABS")) tbl_->slabs_enabled.store(0);
     if (const char *e = getenv("OCM_DAEMON_NODE_LOCAL")) node_local_ = atoi(e) != 0;
 
-    if (host_bytes) {
+    // Host pool.  With a GPU: one pinned VMM allocation on the GPU's NUMA node, handed to applications by file
+    // descriptor (they map it without pinning anything again).  Without one, or if the driver refuses
+    // (OCM_HOST_POOL=shm forces it): a shared-memory segment that every process pins for itself.
+    const char *hp = getenv("OCM_HOST_POOL");
+    if (host_bytes && gpu_ >= 0 && !(hp && !strcmp(hp, "shm"))) {
+        const uint64_t want = tbl_->pool[TIER_HOST].bytes;
+        if (gpu::host_pool_create(host_numa_, want, gpu_, &host_vmm_, &err) && host_vmm_.bytes >= want) {
+            host_map_.base = host_vmm_.ptr;
+            host_map_.bytes = want;
+            // fresh pools start zeroed; the GPU writes the zeros (PCIe rate; a first CPU pass over the mapping runs
+            // at ~2 GB/s, it faults every page into this process)
+            ocmk::launch_fill(host_vmm_.ptr, want, 0, (cudaStream_t)scrub_stream_);
+            cudaStreamSynchronize((cudaStream_t)scrub_stream_);
+            tbl_->host_share_mode = GPU_SHARE_VMM_FD;
+            tbl_->host_numa_node = host_vmm_.owner_dev;
+            shm_unlink(shm_host_pool_name(rank_).c_str());       // no stale segment of an earlier incarnation
+        } else {
+            if (host_vmm_.ptr) gpu::pool_release(&host_vmm_);
+            LOGW("host pool as a VMM allocation refused (%s): shared memory instead", err.c_str());
+        }
+    }
+    if (host_bytes && !host_vmm_.ptr) {
         if (!shm_create(shm_host_pool_name(rank_), tbl_->pool[TIER_HOST].bytes, true, &host_map_, &err)) {
             LOGE("%s", err.c_str());
             return -ENOMEM;
@@ -188,9 +214,9 @@ int Daemon::setup_pools() {
     }
     if (gpu_ >= 0 && !gpu::host_register(tbl_map_.base, tbl_map_.bytes, &err))
         LOGW("tables not device-visible: %s", err.c_str());
-    LOGI("rank %d pools: gpu=%d %llu B (%s), host %llu B", rank_, gpu_, (unsigned long long)gpu_bytes,
+    LOGI("rank %d pools: gpu=%d %llu B (%s), host %llu B (%s)", rank_, gpu_, (unsigned long long)gpu_bytes,
          gpu_pool_.mode == GPU_SHARE_VMM_FD ? "vmm-fd" : gpu_pool_.mode == GPU_SHARE_CUDA_IPC ? "cuda-ipc" : "none",
-         (unsigned long long)host_bytes);
+         (unsigned long long)host_bytes, host_vmm_.ptr ? "pinned vmm-fd" : "shared memory");
     return 0;
 }
 
@@ -958,6 +984,12 @@ void Daemon::on_uds_accept() {
             rp.mode = gpu_pool_.ptr ? gpu_pool_.mode : GPU_SHARE_NONE;
             if (!gpu_pool_.ptr) rp.err = OCM_ENOGPU;
             else if (gpu_pool_.mode == GPU_SHARE_VMM_FD) pass = gpu_pool_.share_fd;
+        } else if (rq.what == UDS_GET_HOST_POOL) {
+            rp.bytes = host_vmm_.bytes;
+            rp.owner_dev = host_vmm_.owner_dev;       // NUMA node
+            rp.mode = host_vmm_.ptr ? GPU_SHARE_VMM_FD : GPU_SHARE_NONE;
+            if (host_vmm_.ptr) pass = host_vmm_.share_fd;
+            else rp.err = OCM_EUNSUPPORTED;
         } else if (rq.what == UDS_GET_MULTICAST) {
             // rank 0 hands its multicast object to the other daemons and to applications
             if (rank_ == 0 && mc_.fd >= 0) {
@@ -1122,6 +1154,14 @@ void Daemon::scrub_loop() {
                 if (t == TIER_GPU && gpu_pool_.ptr) {
                     for (auto &b : blocks)
                         ocmk::launch_fill((char *)gpu_pool_.ptr + b.offset, b.bytes, 0, (cudaStream_t)scrub_stream_);
+                    cudaStreamSynchronize((cudaStream_t)scrub_stream_);
+                } else if (t == TIER_HOST && host_vmm_.ptr) {
+                    for (auto &b : blocks) {
+                        const Region *rec = table_region_rec(tbl_, t, b.region);
+                        uint64_t n = std::min<uint64_t>(b.bytes, ((rec ? rec->bytes : b.bytes) + 4095) & ~4095ull);
+                        if (n <= (64u << 10)) memset((char *)host_map_.base + b.offset, 0, n);
+                        else ocmk::launch_fill((char *)host_map_.base + b.offset, n, 0, (cudaStream_t)scrub_stream_);
+                    }
                     cudaStreamSynchronize((cudaStream_t)scrub_stream_);
                 } else if (t == TIER_HOST && host_map_.base) {
                     for (auto &b : blocks) {

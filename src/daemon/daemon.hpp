@@ -98,6 +98,7 @@ class Daemon {
     topo::GpuTopo topo_;                    // what the runtime and sysfs know about gpu_ (peer row, NUMA node, ...)
     int host_numa_ = -1;                    // NUMA node the pinned host pool is bound to (-1: not bound)
     ShmMapping tbl_map_, host_map_, cluster_map_;
+    gpu::PoolMapping host_vmm_;             // the host pool as a pinned VMM allocation (host_map_.base aliases its mapping)
     TableHeader *tbl_ = nullptr;
     ClusterTable *cluster_ = nullptr;       // rank 0 only (owner)
     gpu::PoolMapping gpu_pool_;

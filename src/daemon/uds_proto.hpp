@@ -1,6 +1,6 @@
 // Tiny request/reply exchanged on the daemon's abstract unix socket.  The reply
-// may carry one file descriptor (the CUDA VMM export of the rank's HBM pool, or
-// rank 0's multicast object).
+// may carry one file descriptor (the CUDA VMM export of the rank's HBM pool or of
+// its pinned host pool, or rank 0's multicast object).
 #pragma once
 #include "../ipc/sock.hpp"
 #include <cstdint>
@@ -10,7 +10,7 @@
 namespace ocm {
 
 constexpr uint32_t kUdsMagic = 0x4F434D55u; // "OCMU"
-enum UdsWhat : uint32_t { UDS_GET_GPU_POOL = 1, UDS_GET_MULTICAST = 2 };
+enum UdsWhat : uint32_t { UDS_GET_GPU_POOL = 1, UDS_GET_MULTICAST = 2, UDS_GET_HOST_POOL = 3 };
 
 struct UdsRequest {
     uint32_t magic;

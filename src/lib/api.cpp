@@ -205,7 +205,26 @@ RankView *get_view(int rank, bool with_gpu) {
             return nullptr;
         }
         v->hdr = h;
-        if (h->pool[TIER_HOST].bytes) {
+        if (h->pool[TIER_HOST].bytes && h->host_share_mode == GPU_SHARE_VMM_FD) {
+            // pinned VMM allocation of that rank's daemon: one descriptor, mapped for our GPU and the CPU; nothing to pin
+            UdsReply rp;
+            int fd = -1;
+            if (c.device < 0) {
+                LOGW("rank %d host pool is a CUDA VMM allocation: this process has no GPU and cannot map it", rank);
+            } else if (!uds_fetch(uds_name(rank), UDS_GET_HOST_POOL, c.device, &rp, &fd) || rp.err || fd < 0) {
+                LOGW("rank %d did not hand out its host pool", rank);
+            } else {
+                DeviceGuard dg(c.device);
+                if (gpu::host_pool_import_fd(fd, rp.bytes, h->host_numa_node, c.device, &v->host_vmm, &err)) {
+                    v->host_map.base = v->host_vmm.ptr;
+                    v->host_map.bytes = h->pool[TIER_HOST].bytes;
+                    v->host_registered = true;
+                } else {
+                    LOGW("rank %d host pool: %s", rank, err.c_str());
+                }
+            }
+            if (fd >= 0) close(fd);
+        } else if (h->pool[TIER_HOST].bytes) {
             if (!shm_open_existing(shm_host_pool_name(rank), &v->host_map, &err))
                 LOGW("rank %d host pool: %s", rank, err.c_str());
         }
@@ -231,7 +250,7 @@ RankView *get_view(int rank, bool with_gpu) {
 // 192 GiB to pin per process).  Pieces: ctx.hpp host_reg_chunk (the whole pool up to 2 GiB, else 256 MiB; OCM_HOST_REG_CHUNK), aligned to the pool's base.
 static void view_host_ready(RankView *v, uint64_t offset, uint64_t bytes) {
     Ctx &c = ctx();
-    if (!v || !v->host_map.base || c.device < 0 || !bytes) return;
+    if (!v || !v->host_map.base || c.device < 0 || !bytes || v->host_vmm.ptr) return;
     const uint64_t total = v->host_map.bytes, chunk = host_reg_chunk(v->hdr->pool[TIER_HOST].bytes);
     if (offset >= total) return;
     if (bytes > total - offset) bytes = total - offset;
@@ -255,6 +274,10 @@ static void view_host_ready(RankView *v, uint64_t offset, uint64_t bytes) {
 
 static void drop_view(RankView &v) {
     if (v.gpu.ptr) gpu::pool_release(&v.gpu);
+    if (v.host_vmm.ptr) {
+        gpu::pool_release(&v.host_vmm);
+        v.host_map = ShmMapping();
+    }
     if (v.host_map.base) {
         if (v.host_registered) {
             const uint64_t chunk = host_reg_chunk(v.hdr ? v.hdr->pool[TIER_HOST].bytes : v.host_map.bytes);

@@ -218,7 +218,8 @@ static int single_copy(const Side &dst, uint64_t dst_off, const Side &src, uint6
     // pool (ctx.hpp host_reg_chunk) and one cudaMemcpyAsync must stay inside one registration: cut at the boundaries.
     note_other_gpu_op();
     const Side &h = dst.tier == TIER_HOST ? dst : src;
-    const bool pool_host = h.backing == SIDE_POOL || h.backing == SIDE_ATTACHED;
+    const bool pool_host = (h.backing == SIDE_POOL || h.backing == SIDE_ATTACHED) &&
+                           !(h.hdr && h.hdr->host_share_mode == GPU_SHARE_VMM_FD);   // a VMM pool is one mapping
     const uint64_t chunk = host_reg_chunk(pool_host && h.hdr ? h.hdr->pool[TIER_HOST].bytes : 0);
     const cudaMemcpyKind kind = dst.tier == TIER_GPU ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
     uint64_t pos = h.offset + (dst.tier == TIER_HOST ? dst_off : src_off);      // position inside the pool

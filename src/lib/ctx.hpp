@@ -27,6 +27,7 @@ struct RankView {
     ShmMapping   tbl_map;
     TableHeader *hdr = nullptr;
     ShmMapping   host_map;
+    gpu::PoolMapping host_vmm;              // host pool imported as a pinned VMM allocation (host_map.base aliases it)
     bool         host_registered = false;   // at least one chunk of the host pool is pinned + mapped for our GPU
     std::vector<uint8_t> host_chunk_reg;    // per chunk of the host pool: registered for this process (api.cpp)
     bool         gpu_tried = false;

@@ -265,5 +265,28 @@ print("HOST PIECES OK")
 def test_host_pool_pinned_in_pieces():
     """OCM_HOST_REG_CHUNK=2M: a process pins a rank's host pool piece by piece as its blocks are used; blocks that span
     pieces registered at different times still copy to and from the GPU (the library cuts its copies at the seams)."""
-    with _cluster(gpu_bytes=256 << 20, host_bytes=64 << 20) as cl:
+    with _cluster(gpu_bytes=256 << 20, host_bytes=64 << 20, extra_env={"OCM_HOST_POOL": "shm"}) as cl:
         assert "HOST PIECES OK" in _ok(run_py(cl, 0, HOST_PIECES, env_extra={"OCM_HOST_REG_CHUNK": str(2 << 20)}))
+
+
+def test_host_pool_is_a_pinned_vmm_allocation_by_default():
+    """With a GPU the daemon creates its host pool as a pinned CUDA VMM allocation and hands it out by descriptor:
+    the application maps it without pinning anything, CPU and GPU both see the bytes, fresh blocks are zero."""
+    code = r"""
+import torch, oncilla_b200 as ocm
+from oncilla_b200 import ops
+ocm.init()
+h = ocm.alloc(ocm.OCM_REMOTE_HOST, 1 << 20, 5 << 20)
+f = h.remote_tensor()
+assert int(f.sum()) == 0                                    # CPU reads zeros
+ops.fill(h.local_tensor(), 0x1122334455667788); h.put(1 << 20)
+assert ops.verify(f[: 1 << 20], 0x1122334455667788, 1 << 20) == 0
+g = ocm.alloc(ocm.OCM_LOCAL_GPU, 1 << 20)
+ocm.copy(g, h, 1 << 20, src_offset=0)                      # host window -> GPU through the library
+assert ops.verify(g.local_tensor(), 0x1122334455667788, 1 << 20) == 0
+h.free(); g.free(); ocm.tini()
+print("VMM HOST OK")
+"""
+    with _cluster(gpu_bytes=256 << 20, host_bytes=64 << 20, log_level="info") as cl:
+        assert "VMM HOST OK" in _ok(run_py(cl, 0, code))
+        assert "pinned vmm-fd" in cl.read_log(0), cl.read_log(0)[-600:]
