@@ -143,6 +143,27 @@ int main() {
     cudaDeviceSynchronize();
     unsigned long long hb = 0;
     cudaMemcpy(&hb, bad, 8, cudaMemcpyDeviceToHost);
+    // gather-reduce through the switch: every replica holds 1.5f, the multicast load returns the sum over the GPUs
+    for (int d = 0; d < ndev; ++d) ocmk::launch_fill((void *)uni[d], mp.size, 0x3FC000003FC00000ull, 0);
+    cudaDeviceSynchronize();
+    float *red;
+    cudaMalloc(&red, mp.size);
+    ocmk::launch_get_reduce_f32(red, (const void *)mcva, mp.size, 0);
+    cudaDeviceSynchronize();
+    cudaEventRecord(e0);
+    for (int i = 0; i < 10; ++i) ocmk::launch_get_reduce_f32(red, (const void *)mcva, mp.size, 0);
+    cudaEventRecord(e1);
+    cudaError_t re = cudaDeviceSynchronize();
+    float rms = 0;
+    cudaEventElapsedTime(&rms, e0, e1);
+    float probe[2] = {0, 0};
+    cudaMemcpy(&probe[0], red, 4, cudaMemcpyDeviceToHost);
+    cudaMemcpy(&probe[1], red + mp.size / 4 - 1, 4, cudaMemcpyDeviceToHost);
+    const bool red_ok = re == cudaSuccess && probe[0] == 1.5f * ndev && probe[1] == 1.5f * ndev;
+    printf("{\"kind\": \"mc_probe_reduce\", \"ok\": %s, \"n_gpus\": %d, \"bytes\": %zu, \"us_per_reduce_get\": %.1f, "
+           "\"result_GBps\": %.1f, \"gathered_GBps\": %.1f}\n",
+           red_ok ? "true" : "false", ndev, (size_t)mp.size, rms * 100.0, mp.size / (rms / 10 * 1e-3) / 1e9,
+           ndev * mp.size / (rms / 10 * 1e-3) / 1e9);
     printf("{\"kind\": \"mc_probe\", \"ok\": %s, \"n_gpus\": %d, \"bytes\": %zu, \"gran_rec\": %zu, \"gran_min\": %zu, "
            "\"launch\": \"%s\", \"sync\": \"%s\", \"bad_words\": %llu, \"us_per_put\": %.1f, \"src_GBps\": %.1f, "
            "\"delivered_GBps\": %.1f}\n",
