@@ -105,11 +105,13 @@ class TorchrunCluster:
         self.barrier()
         self.cl = LocalCluster(self.world, ns=f"job{tag}", nodefile=str(nodefile), ranks=[self.rank],
                                extra_env=None if self.gpu else {"OCM_NO_GPU": "1"})
+        # creating, zeroing and (in the shared-memory form) pinning the pools takes time in proportion to their size
+        wait = 60.0 + 4.0 * (self.host_bytes >> 30) + 0.5 * (self.gpu_bytes >> 30)
         if self.rank == 0:
-            self.cl.start()
+            self.cl.start(timeout=wait)
         self.barrier()
         if self.rank != 0:
-            self.cl.start()
+            self.cl.start(timeout=wait)
         self.barrier()
         self.cl.apply_env(self.rank)
         if self.gpu:
