@@ -242,7 +242,10 @@ def test_cast_f32_bf16_roundtrip_matches_torch():
 
 
 @pytest.mark.parametrize("n_dst", [2, 4, 8])
-def test_put_replicated_cluster_multicast(n_dst):
+def test_put_replicated_cluster_kernel(n_dst):
+    """K6 through the raw-pointer ABI: one CTA of a cluster per destination, every CTA bulk-loads its own tiles (the
+    cluster-shared form needs a source the library knows to be local: test_gpu_resilience.py, replicated put
+    without NVLS)."""
     n = (6 << 20) + 16
     src = rnd_bytes(n, seed=n_dst)
     dsts = [torch.zeros(n, dtype=torch.uint8, device="cuda") for _ in range(n_dst)]
