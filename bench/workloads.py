@@ -112,7 +112,8 @@ def main():
                                       "pass": pass_no,  # pass 0 also pins the host-pool pieces it touches (once per process)
                                       "total_bytes": world * args.sort_keys * 8, "chunk_keys": args.sort_chunk,
                                       "runs_per_rank": s["n_runs"], "slices_per_partition": s["slices_per_partition"],
-                                      "seconds_max": round(worst, 4), "phase1_run_formation_s": round(p1, 4),
+                                      "seconds_max": round(worst, 4), "setup_map_pools_s_rank0": round(s["setup_s"], 4),
+                                      "phase1_run_formation_s": round(p1, 4),
                                       "phase2_gather_merge_s": round(p2, 4),
                                       "Mkeys_per_s_aggregate": round(world * args.sort_keys / worst / 1e6, 1),
                                       "GBps_aggregate": round(world * args.sort_keys * 8 / worst / 1e9, 2),

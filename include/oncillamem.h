@@ -136,6 +136,11 @@ uint64_t ocm_alloc_id(ocm_alloc_t a);
  * this process, and the bytes per slab.  Striped: logical offset o lives in slab o / slab_bytes. */
 void    *ocm_slab_ptr(ocm_alloc_t a, int rank);
 uint64_t ocm_slab_bytes(ocm_alloc_t a);
+/* Map every rank's tables and pools into this process NOW instead of at the first allocation / attach that needs
+ * them (mapping a 100 GiB peer pool takes seconds, once per process; an application with a timed phase calls this
+ * during set-up).  tiers: bit 0 = HBM pools, bit 1 = host pools.  Returns the number of ranks whose requested pools
+ * are mapped, or a negative ocm_err. */
+int      ocm_prefetch_views(unsigned tiers);
 /* NVLS: 1 once the daemons have bound the multicast region and this process has mapped it; replicated
  * allocations made after that are multicast-backed (one multimem.st stream reaches every GPU). */
 int      ocm_multicast_ready(void);

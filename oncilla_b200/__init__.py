@@ -17,9 +17,8 @@ from ._native import (ALLOC_NO_WINDOW, ALLOC_NO_ZERO, ALLOC_SLOW_PATH, DT_BF16, 
                       OCM_LOCAL_GPU, OCM_LOCAL_HOST, OCM_REMOTE_GPU, OCM_REMOTE_HOST, OCM_REMOTE_RDMA, OCM_REMOTE_RMA,
                       OCM_REPLICATED_GPU, OCM_STRIPED_GPU, POLICY_DEFAULT, POLICY_EXPLICIT, POLICY_LEAST_LOADED,
                       POLICY_NEIGHBOUR, POLICY_ROUND_ROBIN, POLICY_SELF, OcmError, build_native)
-from .api import (Allocation, alloc, attach, copy, copy_strided, device, init, multicast_ready, num_ranks, quiet, rank,
-                  server_stats,
-                  stats, tini)
+from .api import (Allocation, alloc, attach, copy, copy_strided, device, init, multicast_ready, num_ranks,
+                  prefetch_views, quiet, rank, server_stats, stats, tini)
 from .cluster import LocalCluster, write_nodefile
 
 __all__ = [n for n in dir() if not n.startswith("_")]

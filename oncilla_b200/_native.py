@@ -144,6 +144,7 @@ _sig("ocm_alloc_id", C.c_uint64, ocm_alloc_t)
 _sig("ocm_slab_ptr", C.c_void_p, ocm_alloc_t, C.c_int)
 _sig("ocm_slab_bytes", C.c_uint64, ocm_alloc_t)
 _sig("ocm_multicast_ready", C.c_int)
+_sig("ocm_prefetch_views", C.c_int, C.c_uint)
 _sig("ocm_is_multicast", C.c_int, ocm_alloc_t)
 _sig("ocm_copy_async", C.c_int, ocm_alloc_t, ocm_alloc_t, P(ocm_params), C.c_void_p)
 _sig("ocm_copy_onesided_async", C.c_int, ocm_alloc_t, P(ocm_params), C.c_void_p)

@@ -87,12 +87,15 @@ def _u(t):
 
 
 def run(keys_per_rank: int = 1 << 22, chunk_keys: int = 1 << 20, parts_per_rank: int | None = None,
-        hbm_budget: int = 1 << 62, final: str = "merge", check: bool = True, collaborate: bool = True) -> dict:
+        hbm_budget: int = 1 << 62, final: str = "merge", check: bool = True, collaborate: bool = True,
+        prefetch: bool = True) -> dict:
     """Sort ``keys_per_rank`` synthetic keys per rank into one global order (rank r ends up owning partitions
     ``r * parts_per_rank ...``).  ``chunk_keys`` keys fit one working buffer; ``hbm_budget`` bytes of this rank's runs
     and output may live in peer HBM, the rest spills to pinned host pools.  ``final``: "merge" (k-way merge of the
     gathered sorted slices) or "sort" (radix sort of the gathered partition, the round-1 behaviour, for comparison).
-    ``collaborate=False`` ignores ``torch.distributed``: this process sorts its own keys alone."""
+    ``collaborate=False`` ignores ``torch.distributed``: this process sorts its own keys alone.
+    ``prefetch``: map every rank's pools before the clock starts (once per process; reported as ``setup_s``) - the
+    sort touches all of them, and mapping seven 100 GiB peer pools on first use cost 29 s of a 41 s first pass."""
     import torch
 
     dist = _dist() if collaborate else None
@@ -135,6 +138,12 @@ def run(keys_per_rank: int = 1 << 22, chunk_keys: int = 1 << 20, parts_per_rank:
         ops._check(ops.lib.ocmk_checksum(ops.C.c_void_p(t.data_ptr()), t.numel() * 8, ops.C.c_void_p(acc.data_ptr()),
                                          ops._stream()), "ocmk_checksum")
 
+    t_setup = time.time()
+    if prefetch:
+        api.prefetch_views()
+        if dist:
+            dist.barrier()
+    setup_s = time.time() - t_setup
     try:
         # ---- splitters: a sample of every rank's stream -> P - 1 global splitters (the same on every rank) ----------
         t_start = time.time()
@@ -249,7 +258,7 @@ def run(keys_per_rank: int = 1 << 22, chunk_keys: int = 1 << 20, parts_per_rank:
                     last = lastk
         seconds = t_end - t_start
         return {"keys_per_rank": keys_per_rank, "world": world, "n_runs": n_runs, "parts_per_rank": S, "final": final,
-                "seconds": seconds, "phase1_s": t_runs - t_start, "phase2_s": t_end - t_runs,
+                "seconds": seconds, "setup_s": setup_s, "phase1_s": t_runs - t_start, "phase2_s": t_end - t_runs,
                 "mkeys_per_s": world * keys_per_rank / seconds / 1e6,
                 "bytes_in_hbm": runs_spill.bytes["hbm"] + out_spill.bytes["hbm"],
                 "bytes_in_host": runs_spill.bytes["host"] + out_spill.bytes["host"],

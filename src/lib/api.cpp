@@ -928,6 +928,21 @@ void *ocm_slab_ptr(ocm_alloc_t a, int rank) {
 }
 uint64_t ocm_slab_bytes(ocm_alloc_t a) { return valid_handle(a) ? a->stripe_bytes : 0; }
 
+int ocm_prefetch_views(unsigned tiers) {
+    Ctx &c = ctx();
+    if (!c.inited) return -OCM_ENODAEMON;
+    int n = 0;
+    for (int r = 0; r < c.n_ranks; ++r) {
+        RankView *v = get_view(r, (tiers & 1u) != 0 && c.device >= 0);
+        if (!v) continue;
+        bool ok = true;
+        if ((tiers & 1u) && v->hdr->pool[TIER_GPU].bytes && !v->gpu.ptr) ok = false;
+        if ((tiers & 2u) && v->hdr->pool[TIER_HOST].bytes && !v->host_map.base) ok = false;
+        n += ok;
+    }
+    return n;
+}
+
 int ocm_multicast_ready(void) { return ctx().inited && ensure_mc() ? 1 : 0; }
 int ocm_is_multicast(ocm_alloc_t a) { return valid_handle(a) && a->mc ? 1 : 0; }
 

@@ -759,3 +759,18 @@ print("RESULT " + json.dumps({"ranks": sorted(ranks), "mid": mid, "end": end, "u
         res = json.loads(out.split("RESULT ", 1)[1])
         assert res["ranks"] == [2], res                      # neighbour policy from rank 1
         assert sum(res["mid"]) >= 40 and res["end"] == [0, 0, 0] and res["used"] == [0, 0, 0], res
+
+
+def test_prefetch_views_maps_every_rank(cluster2):
+    """ocm_prefetch_views maps all ranks' tables and host pools at once (set-up time) instead of at first use."""
+    code = r"""
+import oncilla_b200 as ocm
+ocm.init()
+n = ocm.prefetch_views(gpu=False, host=True)
+assert n == ocm.num_ranks() == 2, n
+assert ocm.prefetch_views(gpu=False, host=True) == 2          # idempotent
+a = ocm.alloc(ocm.OCM_REMOTE_HOST, 4096, 4096); a.put(64); a.free()
+ocm.tini()
+print("PREFETCH OK")
+"""
+    assert "PREFETCH OK" in _ok(run_py(cluster2, 0, code))
