@@ -30,6 +30,18 @@ int main() {
         ocm::copy(peer, src, n);                                // lands in pair's far side, counted by its signal
         if (pair.signal() != 2) throw std::runtime_error("the peer's copy was not counted");
 
+        // three puts as one batch (one kernel launch when a GPU side is involved), counted one by one
+        struct ocm_params b[3] = {};
+        for (int i = 0; i < 3; ++i) {
+            b[i].src_offset = b[i].dest_offset = (uint64_t)i * 4096;
+            b[i].bytes = 4096;
+            b[i].op_flag = 1;
+        }
+        pair.batch(b, 3);
+        ocm_quiet();
+        if (pair.signal() != 5) throw std::runtime_error("the batch was not counted put by put");
+        if (ocm::prefetch_views(false, true) < 1) throw std::runtime_error("prefetch_views");
+
         // ownership moves, errors are exceptions
         std::vector<ocm::Allocation> many;
         for (int i = 0; i < 8; ++i) many.emplace_back(OCM_REMOTE_HOST, 4096, 65536);

@@ -118,6 +118,16 @@ class Allocation {
         detail::check(ocm_copy_onesided_async(h_, &p, stream), "ocm_copy_onesided_async");
     }
 
+    void get_async(uint64_t bytes, void *stream, uint64_t src_offset = 0, uint64_t dest_offset = 0) {
+        struct ocm_params p = {};
+        p.src_offset = src_offset, p.dest_offset = dest_offset, p.bytes = bytes, p.op_flag = 0;
+        detail::check(ocm_copy_onesided_async(h_, &p, stream), "ocm_copy_onesided_async");
+    }
+    // n puts / gets of this allocation in ONE kernel launch (entry.op_flag: 1 = put, 0 = get); stream-ordered
+    void batch(const struct ocm_params *entries, int n, void *stream = nullptr) {
+        detail::check(ocm_copy_onesided_batch(h_, entries, n, stream), "ocm_copy_onesided_batch");
+    }
+
     uint64_t signal() const {
         uint64_t v = 0;
         detail::check(ocm_signal_read(h_, &v), "ocm_signal_read");
@@ -149,6 +159,13 @@ inline void copy(Allocation &dst, Allocation &src, uint64_t bytes, uint64_t src_
     p.src_offset_2 = src_offset_2, p.dest_offset_2 = dest_offset_2;
     p.bytes = bytes, p.op_flag = 1;
     detail::check(ocm_copy(dst.handle(), src.handle(), &p), "ocm_copy");
+}
+
+// Map every rank's pools into this process now (set-up) instead of at first use; returns the ranks fully mapped.
+inline int prefetch_views(bool gpu = true, bool host = true) {
+    int r = ocm_prefetch_views((gpu ? 1u : 0u) | (host ? 2u : 0u));
+    if (r < 0) throw Error("ocm_prefetch_views", -r);
+    return r;
 }
 
 } // namespace ocm
