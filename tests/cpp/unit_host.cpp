@@ -14,7 +14,10 @@
 #include "ipc/sock.hpp"
 #include "oracle/oracle.hpp"
 #include "../../include/oncillamem.h"
+#include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <random>
 #include <cstdio>
 #include <cstring>
 #include <map>
@@ -160,8 +163,9 @@ static void t_tables() {
     CHECK(h->pool[TIER_HOST].granule == 4096 && h->pool[TIER_HOST].n_granules == 256);
     CHECK(default_granule(160ull << 30, TIER_GPU) == (1ull << 20)); // 160 GiB pool -> <= 2^18 granules
     BlockRef a, b, c;
-    CHECK(pool_alloc(h, TIER_GPU, 100, 11, 0, &a) == OCM_OK && a.offset == 0 && a.block_bytes == 65536);
-    CHECK(pool_alloc(h, TIER_GPU, 65537, 11, 0, &b) == OCM_OK && b.offset == 65536 && b.block_bytes == 131072);
+    // single granules come from the top of the pool, runs from the bottom (anti-fragmentation, see t_frag)
+    CHECK(pool_alloc(h, TIER_GPU, 100, 11, 0, &a) == OCM_OK && a.offset == 1023 * 65536ull && a.block_bytes == 65536);
+    CHECK(pool_alloc(h, TIER_GPU, 65537, 11, 0, &b) == OCM_OK && b.offset == 0 && b.block_bytes == 131072);
     CHECK(a.id != b.id);
     CHECK(h->pool[TIER_GPU].used_bytes.load() == 3 * 65536 && h->pool[TIER_GPU].live.load() == 2);
     Region *regs = table_regions(h, TIER_GPU);
@@ -186,7 +190,7 @@ static void t_tables() {
         many.push_back(x);
     }
     CHECK(many.size() == 1024 - 3);
-    CHECK(regs[a.region].generation == a.generation + 1); // first-fit wrapped around into the scrubbed hole
+    CHECK(regs[a.region].generation == a.generation + 1); // the scrubbed hole at the top was found too
     CHECK(pool_count_live(h, TIER_GPU) == many.size() + 2);
     CHECK(h->pool[TIER_GPU].used_bytes.load() == h->pool[TIER_GPU].bytes);
     // coalescing: free everything owned by pid 14, then one block spanning all of it fits
@@ -197,9 +201,9 @@ static void t_tables() {
     CHECK(bytes == many.size() * 65536ull);
     CHECK(pool_count_live(h, TIER_GPU) == 2);
     BlockRef big;
-    CHECK(pool_alloc(h, TIER_GPU, (1024 - 4) * 65536ull, 15, 0, &big) == OCM_OK && big.offset == 4 * 65536ull);
+    CHECK(pool_alloc(h, TIER_GPU, (1024 - 4) * 65536ull, 15, 0, &big) == OCM_OK && big.offset == 2 * 65536ull);
     CHECK(pool_alloc(h, TIER_GPU, 2 * 65536, 15, 0, &c) == OCM_ENOMEM);   // only the single-granule hole is left
-    CHECK(pool_alloc(h, TIER_GPU, 65536, 15, 0, &c) == OCM_OK && c.offset == 0);
+    CHECK(pool_alloc(h, TIER_GPU, 65536, 15, 0, &c) == OCM_OK && c.offset == a.offset);
     CHECK(pool_free(h, TIER_GPU, big.region, big.id) == OCM_OK);
     // host tier independent
     BlockRef hb;
@@ -751,10 +755,69 @@ static void t_oracle() {
     for (auto x : tab) CHECK(x == 3);
 }
 
+// Fragmentation: a 1 GiB pool kept 70-85 % full by random allocations of 1 granule ... 64 granules and 1-32 KiB
+// blocks, released in random order (zeroing simulated at once).  Checks that the accounting survives and that large
+// requests still succeed while space exists in runs, and prints the latency of pool_alloc under that load
+// (`unit_host frag`; numbers in profiles/README.md).
+static void t_frag() {
+    std::vector<char> buf;
+    TableHeader *h = fresh_table(buf, 1ull << 30, 1ull << 20);
+    PoolDesc &p = h->pool[TIER_GPU];
+    std::mt19937_64 rng(getenv("FRAG_SEED") ? strtoull(getenv("FRAG_SEED"), nullptr, 0) : 7);
+    std::vector<BlockRef> live;
+    std::vector<double> ns_small, ns_large;
+    uint64_t enomem_large = 0, tries_large = 0;
+    auto scrub = [&] {
+        std::vector<DirtyBlock> d;
+        pool_take_dirty(h, TIER_GPU, &d);
+        for (auto &b : d) pool_release_scrubbed(h, TIER_GPU, b.region);
+    };
+    for (int it = 0; it < 200000; ++it) {
+        const double fill = (double)p.used_bytes.load() / (double)p.bytes;
+        const bool do_alloc = fill < 0.70 || (fill < 0.85 && (rng() & 1));
+        if (do_alloc) {
+            const bool small = getenv("FRAG_NO_SMALL") ? false : (rng() % 4) != 0;
+            const uint64_t bytes = small ? 1024 + rng() % (31 << 10) : p.granule * (1 + rng() % 64);
+            BlockRef b;
+            const auto t0 = std::chrono::steady_clock::now();
+            int err = pool_alloc(h, TIER_GPU, bytes, 33, 0, &b);
+            const double ns = std::chrono::duration<double, std::nano>(std::chrono::steady_clock::now() - t0).count();
+            (small ? ns_small : ns_large).push_back(ns);
+            if (!small) {
+                ++tries_large;
+                enomem_large += err == OCM_ENOMEM;
+            }
+            if (err == OCM_OK) live.push_back(b);
+            else CHECK(err == OCM_ENOMEM);
+        } else if (!live.empty()) {
+            const size_t k = rng() % live.size();
+            CHECK(pool_free(h, TIER_GPU, live[k].region, live[k].id) == OCM_OK);
+            live[k] = live.back();
+            live.pop_back();
+            if ((it & 15) == 0) scrub();
+        }
+    }
+    TableAudit au;
+    CHECK(pool_audit(h, TIER_GPU, &au) == 0);
+    CHECK(pool_count_live(h, TIER_GPU) == live.size());
+    // below 85 % full a request of up to 64 granules (4 MiB of 1 GiB) must almost always find a run
+    CHECK(tries_large > 1000 && enomem_large * 50 < tries_large);
+    for (auto &b : live) CHECK(pool_free(h, TIER_GPU, b.region, b.id) == OCM_OK);
+    scrub();
+    CHECK(p.live.load() == 0 && pool_payload_bytes(h, TIER_GPU) == 0);
+    auto pct = [](std::vector<double> &v, double q) {
+        std::sort(v.begin(), v.end());
+        return v.empty() ? 0.0 : v[(size_t)(q * (v.size() - 1))];
+    };
+    printf("frag: %zu small allocs p50 %.0f ns p99 %.0f ns; %zu large allocs p50 %.0f ns p99 %.0f ns; large ENOMEM %llu of %llu\n",
+           ns_small.size(), pct(ns_small, 0.5), pct(ns_small, 0.99), ns_large.size(), pct(ns_large, 0.5), pct(ns_large, 0.99),
+           (unsigned long long)enomem_large, (unsigned long long)tries_large);
+}
+
 int main(int argc, char **argv) {
     std::string which = argc > 1 ? argv[1] : "all";
     std::map<std::string, void (*)()> suites = {
-        {"msg", t_msg}, {"nodefile", t_nodefile}, {"nodefile_numa", t_nodefile_numa}, {"ring", t_ring}, {"tables", t_tables}, {"tables_mt", t_tables_mt}, {"slabs", t_slabs},
+        {"msg", t_msg}, {"nodefile", t_nodefile}, {"nodefile_numa", t_nodefile_numa}, {"ring", t_ring}, {"tables", t_tables}, {"tables_mt", t_tables_mt}, {"slabs", t_slabs}, {"frag", t_frag},
         {"governor", t_governor}, {"topo", t_topo}, {"pmsg", t_pmsg}, {"sock", t_sock}, {"oracle", t_oracle}};
     int ran = 0;
     for (auto &kv : suites) {
