@@ -30,6 +30,13 @@ inline uint64_t bits(unsigned lo, unsigned hi) {
     return m & ~((1ull << lo) - 1);
 }
 
+// p.hint must never stay above a granule that has just become free
+inline void hint_lower(std::atomic<uint64_t> &hint, uint64_t region) {
+    uint64_t h = hint.load(std::memory_order_relaxed);
+    while (region < h && !hint.compare_exchange_weak(h, region, std::memory_order_acq_rel, std::memory_order_relaxed)) {
+    }
+}
+
 void bitmap_clear(std::atomic<uint64_t> *bm, uint64_t start, uint64_t n) {
     uint64_t i = start, end = start + n;
     while (i < end) {
@@ -514,13 +521,30 @@ static int granule_alloc(TableHeader *h, int tier, uint64_t bytes, int pid, int 
     if (n == 1) {
         start = find_one_down(bm, N);
         if (start == UINT64_MAX) return OCM_ENOMEM;
-    } else {
-        uint64_t hint = p.hint.load(std::memory_order_relaxed);
+    } else if (n < kFirstFitMinGranules) {
+        // short runs: next fit from a rotating start - cheapest search, and concurrent allocators do not meet on the
+        // same bitmap words
+        uint64_t hint = p.rot_hint.load(std::memory_order_relaxed);
         if (hint >= N) hint = 0;
         start = find_run(bm, hint, N, n);
         if (start == UINT64_MAX && hint) start = find_run(bm, 0, std::min<uint64_t>(N, hint + n), n);
         if (start == UINT64_MAX) return OCM_ENOMEM;
-        p.hint.store(start + n >= N ? 0 : start + n, std::memory_order_relaxed);
+        p.rot_hint.store(start + n >= N ? 0 : start + n, std::memory_order_relaxed);
+    } else {
+        // long runs: first fit from the bottom, so that they pack towards low addresses and long runs stay available
+        // (unit_host frag, 1 GiB pool 70-85 % full, random mix: 14 % of run requests refused with one rotating next
+        // fit for everything, 1 % with single granules moved to the top, 0.03 % with this split; first fit for every
+        // run: 0 %, but 3x the search time at that occupancy and all allocators meeting on the lowest free words).
+        // p.hint is a lower bound of the lowest free granule, so a full prefix is skipped without reading it; frees
+        // lower it (hint_lower), the search raises it.  A stale bound can only hide space, never hand out a taken
+        // granule - hence the second search from 0 before giving up.
+        uint64_t h0 = p.hint.load(std::memory_order_acquire);
+        if (h0 >= N) h0 = 0;
+        const uint64_t first = next_free(bm, h0, N);
+        start = first + n <= N ? find_run(bm, first, N, n) : UINT64_MAX;
+        if (first > h0) p.hint.compare_exchange_strong(h0, first, std::memory_order_acq_rel, std::memory_order_relaxed);
+        if (start == UINT64_MAX && h0) start = find_run(bm, 0, N, n);
+        if (start == UINT64_MAX) return OCM_ENOMEM;
     }
 
     Region *regs = table_regions(h, tier);
@@ -575,6 +599,7 @@ int pool_free(TableHeader *h, int tier, uint32_t region, uint64_t id) {
         stack_push(p.dirty_head, regs, region);
     } else {
         bitmap_clear(table_bitmap(h, tier), region, n);
+        hint_lower(p.hint, region);
     }
     return OCM_OK;
 }
@@ -633,6 +658,7 @@ void pool_release_scrubbed(TableHeader *h, int tier, uint32_t region) {
     p.dirty_bytes.fetch_sub((uint64_t)n * p.granule, std::memory_order_relaxed);
     r.state.store(REGION_FREE, std::memory_order_release);
     bitmap_clear(table_bitmap(h, tier), region, n);
+    hint_lower(p.hint, region);
 }
 
 uint64_t pool_scrub_host_inline(TableHeader *h, void *host_pool_base) {

@@ -70,6 +70,9 @@ static_assert(sizeof(Region) == 64, "one cache line per region");
 // incarnation of slab i and a stale CAS can only ever claim a block that really is free.  Every sub-block has a
 // full Region record of its own (owner, id, generation, completion signals, share/attach state): it is an
 // allocation like any other, named by kSlabFlag | slab << 6 | sub wherever a granule index is expected.
+// Runs of at least this many granules are placed first fit from the bottom of the pool, shorter ones next fit from a
+// rotating start, single granules from the top (tables.cpp granule_alloc; measured in unit_host frag).
+constexpr uint32_t kFirstFitMinGranules = 16;
 constexpr uint32_t kSlabFlag    = 0x80000000u;
 constexpr uint32_t kSlabSubs    = 64;
 constexpr uint32_t kSlabClasses = 6;       // class c: 2^(c+1) sub-blocks of granule >> (c+1) bytes
@@ -114,7 +117,8 @@ struct PoolDesc {
     uint64_t bitmap_offset;    // from segment start; one bit per granule, 1 = taken
     uint32_t bitmap_words;
     uint32_t pad;
-    std::atomic<uint64_t> hint;          // granule where the next search starts (first fit, rotating)
+    std::atomic<uint64_t> hint;          // lower bound of the lowest free granule: where the first-fit search for long runs starts
+    std::atomic<uint64_t> rot_hint;      // where the next-fit search for short runs starts (rotating)
     std::atomic<uint64_t> used_bytes;    // sum of live block bytes
     std::atomic<uint64_t> live;
     std::atomic<uint64_t> total_allocs;

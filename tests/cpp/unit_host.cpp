@@ -800,8 +800,8 @@ static void t_frag() {
     TableAudit au;
     CHECK(pool_audit(h, TIER_GPU, &au) == 0);
     CHECK(pool_count_live(h, TIER_GPU) == live.size());
-    // below 85 % full a request of up to 64 granules (4 MiB of 1 GiB) must almost always find a run
-    CHECK(tries_large > 1000 && enomem_large * 50 < tries_large);
+    // below 85 % full a request of up to 64 granules (4 MiB of 1 GiB) must almost always find a run (< 0.5 % refused)
+    CHECK(tries_large > 1000 && enomem_large * 200 < tries_large);
     for (auto &b : live) CHECK(pool_free(h, TIER_GPU, b.region, b.id) == OCM_OK);
     scrub();
     CHECK(p.live.load() == 0 && pool_payload_bytes(h, TIER_GPU) == 0);
