@@ -7,6 +7,7 @@ reference inc/oncillamem.h:69-89, implementation src/lib.c).
 from __future__ import annotations
 
 import ctypes as C
+import threading
 from typing import Optional
 
 from . import _native as N
@@ -310,16 +311,34 @@ def attach(token: bytes) -> Allocation:
     return a
 
 
+_tls = threading.local()
+
+
+def _scratch_params():
+    """One ``ocm_params`` per thread, reused by the one-sided calls (the library reads it during the call only);
+    building a ctypes structure per message costs as much as the library call itself for small messages."""
+    try:
+        return _tls.p, _tls.ref
+    except AttributeError:
+        _tls.p = N.ocm_params()
+        _tls.ref = C.byref(_tls.p)
+        return _tls.p, _tls.ref
+
+
 def _onesided(a: Allocation, op: int, nbytes, src_offset, dest_offset, stream) -> None:
-    p = N.ocm_params()
-    p.src_offset, p.dest_offset = int(src_offset), int(dest_offset)
-    p.bytes = int(a.local_bytes if nbytes is None else nbytes)
+    p, ref = _scratch_params()
+    p.src_offset = src_offset
+    p.dest_offset = dest_offset
+    p.bytes = a.local_bytes if nbytes is None else nbytes
     p.op_flag = op
+    h = a._h
+    if not h:
+        raise OcmError("allocation already freed", 8)
     if stream == "sync":
-        if lib.ocm_copy_onesided(a.handle, C.byref(p)) != 0:
+        if lib.ocm_copy_onesided(h, ref) != 0:
             raise OcmError("ocm_copy_onesided")
     else:
-        r = lib.ocm_copy_onesided_async(a.handle, C.byref(p), C.c_void_p(_stream_ptr(stream)))
+        r = lib.ocm_copy_onesided_async(h, ref, _stream_ptr(stream))
         if r:
             raise OcmError("ocm_copy_onesided_async", r)
 
