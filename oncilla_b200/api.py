@@ -327,9 +327,9 @@ def _scratch_params():
 
 def _onesided(a: Allocation, op: int, nbytes, src_offset, dest_offset, stream) -> None:
     p, ref = _scratch_params()
-    p.src_offset = src_offset
-    p.dest_offset = dest_offset
-    p.bytes = a.local_bytes if nbytes is None else nbytes
+    p.src_offset = int(src_offset)
+    p.dest_offset = int(dest_offset)
+    p.bytes = int(a.local_bytes if nbytes is None else nbytes)
     p.op_flag = op
     h = a._h
     if not h:
