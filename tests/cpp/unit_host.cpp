@@ -755,6 +755,43 @@ static void t_oracle() {
     for (auto x : tab) CHECK(x == 3);
 }
 
+// Placement by run length (tables.cpp granule_alloc) in a pool whose granule count is not a multiple of 64: the bits
+// past the end of the bitmap's last word are never handed out, singles descend from the top, short runs rotate, long
+// runs pack from the bottom and the lowest-free bound follows frees.
+static void t_placement() {
+    std::vector<char> buf;
+    TableHeader *h = fresh_table(buf, (1000ull << 16) + (29ull << 16), 1ull << 20);   // 1029 granules of 64 KiB
+    h->slabs_enabled.store(0);
+    PoolDesc &p = h->pool[TIER_GPU];
+    CHECK(p.n_granules == 1029 && p.granule == 65536);
+    BlockRef s1, s2, r3, l20, l30;
+    CHECK(pool_alloc(h, TIER_GPU, 1, 5, 0, &s1) == OCM_OK && s1.offset == 1028 * 65536ull);
+    CHECK(pool_alloc(h, TIER_GPU, 65536, 5, 0, &s2) == OCM_OK && s2.offset == 1027 * 65536ull);
+    CHECK(pool_alloc(h, TIER_GPU, 3 * 65536, 5, 0, &r3) == OCM_OK && r3.offset == 0);                 // short run: rotating start
+    CHECK(pool_alloc(h, TIER_GPU, 20 * 65536, 5, 0, &l20) == OCM_OK && l20.offset == 3 * 65536ull);   // long run: lowest free
+    CHECK(pool_alloc(h, TIER_GPU, 30 * 65536, 5, 0, &l30) == OCM_OK && l30.offset == 23 * 65536ull);
+    // free the first long run (no scrubbing in this suite: the bits clear at once): the next long run goes back there
+    h->scrub_enabled.store(0);
+    CHECK(pool_free(h, TIER_GPU, l20.region, l20.id) == OCM_OK);
+    BlockRef l16, l17;
+    CHECK(pool_alloc(h, TIER_GPU, 16 * 65536, 5, 0, &l16) == OCM_OK && l16.offset == 3 * 65536ull);
+    CHECK(pool_alloc(h, TIER_GPU, 17 * 65536, 5, 0, &l17) == OCM_OK && l17.offset == 53 * 65536ull);  // hole of 4 is too small
+    // everything that is left, one granule at a time: exactly the free granules, none past the end
+    size_t singles = 0;
+    uint64_t lowest = ~0ull;
+    for (;;) {
+        BlockRef x;
+        if (pool_alloc(h, TIER_GPU, 65536, 6, 0, &x) != OCM_OK) break;
+        CHECK(x.offset / 65536 < 1029);
+        lowest = std::min(lowest, x.offset / 65536);
+        ++singles;
+    }
+    CHECK(singles == 1029 - 2 - 3 - 30 - 16 - 17 && lowest == 19);
+    CHECK(p.used_bytes.load() == p.bytes);
+    TableAudit au;
+    CHECK(pool_audit(h, TIER_GPU, &au) == 0);
+}
+
 // Fragmentation: a 1 GiB pool kept 70-85 % full by random allocations of 1 granule ... 64 granules and 1-32 KiB
 // blocks, released in random order (zeroing simulated at once).  Checks that the accounting survives and that large
 // requests still succeed while space exists in runs, and prints the latency of pool_alloc under that load
@@ -817,7 +854,7 @@ static void t_frag() {
 int main(int argc, char **argv) {
     std::string which = argc > 1 ? argv[1] : "all";
     std::map<std::string, void (*)()> suites = {
-        {"msg", t_msg}, {"nodefile", t_nodefile}, {"nodefile_numa", t_nodefile_numa}, {"ring", t_ring}, {"tables", t_tables}, {"tables_mt", t_tables_mt}, {"slabs", t_slabs}, {"frag", t_frag},
+        {"msg", t_msg}, {"nodefile", t_nodefile}, {"nodefile_numa", t_nodefile_numa}, {"ring", t_ring}, {"tables", t_tables}, {"tables_mt", t_tables_mt}, {"slabs", t_slabs}, {"frag", t_frag}, {"placement", t_placement},
         {"governor", t_governor}, {"topo", t_topo}, {"pmsg", t_pmsg}, {"sock", t_sock}, {"oracle", t_oracle}};
     int ran = 0;
     for (auto &kv : suites) {
