@@ -9,7 +9,7 @@ import pytest
 
 from conftest import BIN
 
-SUITES = ["msg", "nodefile", "ring", "tables", "tables_mt", "slabs", "governor", "topo", "nodefile_numa", "pmsg", "sock", "oracle"]
+SUITES = ["msg", "nodefile", "ring", "tables", "tables_mt", "slabs", "frag", "placement", "governor", "topo", "nodefile_numa", "pmsg", "sock", "oracle"]
 
 
 def test_daemon_check_mode(tmp_path):
